@@ -1,0 +1,224 @@
+"""Oracle: NumPy restatement of skimage.restoration.denoise_wavelet (0.14.2)
+and the PyWavelets (1.0.3) routines it reaches.  TEST INFRASTRUCTURE ONLY.
+
+PARITY UNPINNED against the real libraries: scikit-image 0.14.2 and
+pywavelets 1.0.3 are pinned in the reference's requirements.txt:151,160 but
+are neither vendored under /root/reference nor installable here (no network).
+The algorithm below restates their published source:
+  skimage/restoration/_denoise.py  (_wavelet_threshold, _bayes_thresh,
+                                    _sigma_est_dwt, denoise_wavelet)
+  skimage/color/colorconv.py       (rgb2ycbcr, ycbcr2rgb)
+  pywt/_multilevel.py              (wavedecn, waverecn), pywt/_thresholding.py
+and is anchored on the reference's call sites (minibatch.py:92-96 - bior1.5,
+automatic levels; test.py_bkp:1913-1916 - db1, wavelet_levels=3).  It is held
+by the property tests in tests/test_oracle_wavelet.py.
+"""
+import numpy as np
+
+_S = 0.7071067811865476
+_C1 = 0.01657281518405971     # sqrt(2) * 3 / 256
+_C2 = 0.12153397801643787     # sqrt(2) * 11 / 128
+
+WAVELETS = {
+    # name: (dec_lo, dec_hi, rec_lo, rec_hi) as PyWavelets lists them
+    "db1": ([_S, _S], [-_S, _S], [_S, _S], [_S, -_S]),
+    "bior1.5": (
+        [_C1, -_C1, -_C2, _C2, _S, _S, _C2, -_C2, -_C1, _C1],
+        [0.0, 0.0, 0.0, 0.0, -_S, _S, 0.0, 0.0, 0.0, 0.0],
+        [0.0, 0.0, 0.0, 0.0, _S, _S, 0.0, 0.0, 0.0, 0.0],
+        [_C1, _C1, -_C2, -_C2, _S, -_S, _C2, _C2, -_C1, -_C1],
+    ),
+}
+WAVELETS["haar"] = WAVELETS["db1"]
+
+
+def dwt_max_level(data_len, filter_len):
+    """pywt.dwt_max_level: floor(log2(data_len / (filter_len - 1)))."""
+    if data_len < filter_len - 1:
+        return 0
+    return int(np.floor(np.log2(data_len / (filter_len - 1.0))))
+
+
+def _take(a, axis, sl):
+    idx = [slice(None)] * a.ndim
+    idx[axis] = sl
+    return a[tuple(idx)]
+
+
+def dwt_axis(x, wavelet, axis):
+    """Single-level DWT along ``axis``, mode='symmetric' (half-sample symmetric
+    extension).  Equals np.convolve(np.pad(x, F-1, 'symmetric'), filt,
+    'valid')[1::2] per line; output length floor((n + F - 1) / 2)."""
+    dec_lo, dec_hi = WAVELETS[wavelet][0], WAVELETS[wavelet][1]
+    F = len(dec_lo)
+    n = x.shape[axis]
+    pad = [(0, 0)] * x.ndim
+    pad[axis] = (F - 1, F - 1)
+    p = np.pad(x, pad, mode="symmetric")
+    m = (n + F - 1) // 2
+    shape = list(x.shape)
+    shape[axis] = m
+    a = np.zeros(shape, np.float64)
+    d = np.zeros(shape, np.float64)
+    for j in range(F):
+        s = _take(p, axis, slice(F - j, F - j + 2 * m, 2))
+        if dec_lo[j] != 0.0:
+            a += dec_lo[j] * s
+        if dec_hi[j] != 0.0:
+            d += dec_hi[j] * s
+    return a, d
+
+
+def idwt_axis(a, d, wavelet, axis):
+    """Single-level inverse along ``axis``: zero-upsample, convolve with the
+    reconstruction filters, add, keep samples [F-2, 2m) (length 2m - F + 2)."""
+    rec_lo, rec_hi = WAVELETS[wavelet][2], WAVELETS[wavelet][3]
+    F = len(rec_lo)
+    m = a.shape[axis]
+    shape = list(a.shape)
+    shape[axis] = 2 * m + F - 1
+    y = np.zeros(shape, np.float64)
+    for j in range(F):
+        idx = [slice(None)] * a.ndim
+        idx[axis] = slice(j, j + 2 * m, 2)
+        if rec_lo[j] != 0.0:
+            y[tuple(idx)] += rec_lo[j] * a
+        if rec_hi[j] != 0.0:
+            y[tuple(idx)] += rec_hi[j] * d
+    return _take(y, axis, slice(F - 2, 2 * m))
+
+
+def wavedec2(x, wavelet, level):
+    """pywt.wavedecn for a 2-D array: [cA_n, {ad,da,dd}_n, ..., {ad,da,dd}_1];
+    first key letter = axis 0."""
+    a = np.asarray(x, np.float64)
+    details = []
+    for _ in range(level):
+        lo0, hi0 = dwt_axis(a, wavelet, 0)
+        aa, ad = dwt_axis(lo0, wavelet, 1)
+        da, dd = dwt_axis(hi0, wavelet, 1)
+        details.append({"ad": ad, "da": da, "dd": dd})
+        a = aa
+    return [a] + details[::-1]
+
+
+def waverec2(coeffs, wavelet):
+    """pywt.waverecn for 2-D; when the running approximation is one sample
+    longer than the next detail band along an axis it is trimmed to fit."""
+    a = coeffs[0]
+    for det in coeffs[1:]:
+        dshape = det["dd"].shape
+        if a.shape != dshape:
+            a = a[tuple(slice(s) for s in dshape)]
+        lo0 = idwt_axis(a, det["ad"], wavelet, 1)
+        hi0 = idwt_axis(det["da"], det["dd"], wavelet, 1)
+        a = idwt_axis(lo0, hi0, wavelet, 0)
+    return a
+
+
+def soft_threshold(data, value):
+    """pywt.threshold(data, value, 'soft') = data * max(1 - value/|data|, 0)."""
+    mag = np.absolute(data)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        t = 1 - value / mag
+        t = t.clip(min=0, max=None)
+        return data * t
+
+
+# --------------------------------------------------------------------------
+# skimage.restoration._denoise (0.14.2)
+# --------------------------------------------------------------------------
+NORM_PPF_075 = 0.6744897501960817          # scipy.stats.norm.ppf(0.75)
+
+
+def sigma_est_dwt(detail_coeffs):
+    """_sigma_est_dwt: MAD of the non-zero finest-level 'dd' coefficients."""
+    dc = detail_coeffs[np.nonzero(detail_coeffs)]
+    return np.median(np.abs(dc)) / NORM_PPF_075
+
+
+def bayes_thresh(details, var):
+    """_bayes_thresh: var / sqrt(max(mean(d*d) - var, eps))."""
+    dvar = np.mean(details * details)
+    eps = np.finfo(details.dtype).eps
+    return var / np.sqrt(max(dvar - var, eps))
+
+
+def auto_levels(shape, wavelet):
+    """wavelet_levels=None branch of _wavelet_threshold."""
+    dlen = len(WAVELETS[wavelet][0])
+    lv = min(dwt_max_level(s, dlen) for s in shape)
+    return max(lv - 3, 1)
+
+
+def wavelet_threshold(image, wavelet="db1", wavelet_levels=None, return_stats=False):
+    """_wavelet_threshold(image, wavelet, method='BayesShrink', mode='soft')."""
+    original_extent = tuple(slice(s) for s in image.shape)
+    if wavelet_levels is None:
+        wavelet_levels = auto_levels(image.shape, wavelet)
+    coeffs = wavedec2(image, wavelet, wavelet_levels)
+    dcoeffs = coeffs[1:]
+    sigma = sigma_est_dwt(dcoeffs[-1]["dd"])
+    var = sigma ** 2
+    threshold = [{key: bayes_thresh(level[key], var) for key in level} for level in dcoeffs]
+    denoised_detail = [{key: soft_threshold(level[key], thresh[key]) for key in level}
+                       for thresh, level in zip(threshold, dcoeffs)]
+    rec = waverec2([coeffs[0]] + denoised_detail, wavelet)[original_extent]
+    if return_stats:
+        return rec, {"sigma": sigma, "threshold": threshold, "levels": wavelet_levels}
+    return rec
+
+
+YCBCR_FROM_RGB = np.array([[65.481, 128.553, 24.966],
+                           [-37.797, -74.203, 112.0],
+                           [112.0, -93.786, -18.214]])
+RGB_FROM_YCBCR = np.linalg.inv(YCBCR_FROM_RGB)
+
+
+def rgb2ycbcr(rgb):
+    """skimage.color.rgb2ycbcr on a float image in [0,1] (BT.601 studio swing)."""
+    arr = np.dot(np.asarray(rgb, np.float64), YCBCR_FROM_RGB.T.copy())
+    arr[..., 0] += 16
+    arr[..., 1] += 128
+    arr[..., 2] += 128
+    return arr
+
+
+def ycbcr2rgb(ycbcr):
+    arr = ycbcr.copy()
+    arr[..., 0] -= 16
+    arr[..., 1] -= 128
+    arr[..., 2] -= 128
+    return np.dot(arr, RGB_FROM_YCBCR.T.copy())
+
+
+def denoise_wavelet(image, wavelet="db1", wavelet_levels=None, return_stats=False):
+    """denoise_wavelet(image, method='BayesShrink', mode='soft', wavelet=...,
+    wavelet_levels=..., multichannel=True, convert2ycbcr=True)
+    (minibatch.py:92-94).  ``image``: uint8 or float64 HxWx3 in the array's own
+    channel order (the reference feeds BGR - quirk Q7 - so do the callers)."""
+    if image.dtype == np.uint8:
+        image = image.astype(np.float64) / 255.0
+    image = np.asarray(image, np.float64)
+    out = rgb2ycbcr(image)
+    stats = []
+    for i in range(3):
+        mn, mx = out[..., i].min(), out[..., i].max()
+        channel = out[..., i] - mn
+        with np.errstate(divide="ignore", invalid="ignore"):
+            channel /= mx - mn
+        res = wavelet_threshold(channel, wavelet, wavelet_levels, return_stats)
+        if return_stats:
+            res, st = res
+            st.update(min=mn, max=mx)
+            stats.append(st)
+        # the inner (single-channel) denoise_wavelet call clips to [0, 1]
+        res = np.clip(res, 0, 1)
+        out[..., i] = res * (mx - mn)
+        out[..., i] += mn
+    out = ycbcr2rgb(out)
+    clip_range = (-1, 1) if image.min() < 0 else (0, 1)
+    out = np.clip(out, *clip_range)
+    if return_stats:
+        return out, stats
+    return out
