@@ -1,0 +1,125 @@
+// b2d_common.cuh - shared device helpers for libb200denoise (sm_100a only).
+//
+// Philox4x32-10 counter-based generator (Salmon et al., SC'11), approximate
+// SFU math wrappers, packed-byte helpers.  No host code here.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#ifndef __CUDA_ARCH__
+#define B2D_ARCH_OK 1
+#elif __CUDA_ARCH__ >= 1000
+#define B2D_ARCH_OK 1
+#else
+#error "libb200denoise is written for sm_100a (B200) only"
+#endif
+
+namespace b2d {
+
+// ---------------------------------------------------------------------------
+// Philox4x32-10.  counter = (c0, c1, c2, c3), key = (k0, k1).
+// Our use: c0 = element-group index inside the image (8 uint8 elements per
+// group), c1 = substream (0 = primary draw, >0 = retries / extra draws),
+// (c2, c3) = global image index; key = seed.
+// ---------------------------------------------------------------------------
+#define B2D_PHILOX_M0 0xD2511F53u
+#define B2D_PHILOX_M1 0xCD9E8D57u
+#define B2D_PHILOX_W0 0x9E3779B9u
+#define B2D_PHILOX_W1 0xBB67AE85u
+
+__host__ __device__ __forceinline__ void philox_round(uint32_t& c0, uint32_t& c1, uint32_t& c2,
+                                                      uint32_t& c3, uint32_t k0, uint32_t k1) {
+  const uint64_t p0 = (uint64_t)B2D_PHILOX_M0 * c0;
+  const uint64_t p1 = (uint64_t)B2D_PHILOX_M1 * c2;
+  const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+  const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+  c1 = (uint32_t)p1;
+  c3 = (uint32_t)p0;
+  c0 = n0;
+  c2 = n2;
+}
+
+__host__ __device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2,
+                                                        uint32_t c3, uint32_t k0, uint32_t k1) {
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    philox_round(c0, c1, c2, c3, k0, k1);
+    k0 += B2D_PHILOX_W0;
+    k1 += B2D_PHILOX_W1;
+  }
+  return make_uint4(c0, c1, c2, c3);
+}
+
+// ---------------------------------------------------------------------------
+// SFU wrappers (one MUFU each, flush-to-zero, no range fix-up code)
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ float fast_lg2(float x) {
+  float y;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float fast_ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float fast_sqrt(float x) {
+  float y;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float fast_sin(float x) {
+  float y;
+  asm("sin.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float fast_cos(float x) {
+  float y;
+  asm("cos.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float fast_rcp(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// 16 random bits -> uniform in (0,1): (k + 0.5) / 65536, exact in fp32
+__device__ __forceinline__ float u16_to_unit(uint32_t k16) {
+  return fmaf((float)k16, 1.0f / 65536.0f, 0.5f / 65536.0f);
+}
+// 32 random bits -> uniform in (0,1): top 24 bits, (k + 0.5) / 2^24
+__device__ __forceinline__ float u32_to_unit(uint32_t k32) {
+  return fmaf((float)(k32 >> 8), 1.0f / 16777216.0f, 0.5f / 16777216.0f);
+}
+
+// Box-Muller on two 16-bit uniforms -> two standard normals
+__device__ __forceinline__ void box_muller16(uint32_t ka, uint32_t kb, float& z0, float& z1) {
+  const float u1 = u16_to_unit(ka);
+  const float th = fmaf((float)kb, 6.283185307179586f / 65536.0f, 3.141592653589793f / 65536.0f);
+  const float r = fast_sqrt(-1.3862943611198906f * fast_lg2(u1));  // sqrt(-2 ln u1)
+  z0 = r * fast_cos(th);
+  z1 = r * fast_sin(th);
+}
+
+// ---------------------------------------------------------------------------
+// byte helpers
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t pack4(uint32_t b0, uint32_t b1, uint32_t b2, uint32_t b3) {
+  return (b0 & 0xffu) | ((b1 & 0xffu) << 8) | ((b2 & 0xffu) << 16) | (b3 << 24);
+}
+__device__ __forceinline__ uint32_t byte_of(uint32_t w, int i) { return (w >> (8 * i)) & 0xffu; }
+
+// trunc(255 * (v / 255.0)) evaluated in float64 exactly as NumPy does for the
+// reference's (255 * img_as_float(img)).astype(uint8) on an untouched pixel.
+// The round trip is exact for every v in 0..255 (checked in tests), so this is
+// the identity; kept as a named function to mark where the reference's ->u8
+// idiom is applied to noise-free values.
+__device__ __forceinline__ uint32_t u8_roundtrip(uint32_t v) { return v; }
+
+// float -> the reference's astype(uint8) of an in-range or wrapping value:
+// truncate toward zero to int32, keep the low byte.
+__device__ __forceinline__ uint32_t wrap_u8(float x) { return ((uint32_t)__float2int_rz(x)) & 0xffu; }
+__device__ __forceinline__ uint32_t wrap_u8(double x) { return ((uint32_t)__double2int_rz(x)) & 0xffu; }
+
+}  // namespace b2d

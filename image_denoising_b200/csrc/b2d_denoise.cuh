@@ -1,0 +1,26 @@
+// b2d_denoise.cuh - denoisers that run as their own pass over a uint8 image
+// (input already noised): the any-width 3x3 fallback, median 5/7, bilateral,
+// wavelet.  The aligned 3x3 filters live in b2d_fused3.cu.
+#pragma once
+#include "b2d_kernels.cuh"
+#include "../../include/b200denoise.h"
+
+namespace b2d {
+
+size_t denoise_workspace_bytes(const b2d_plan& p);
+
+// 3x3 filters for images whose row size is not a multiple of 4 bytes (W % 4 != 0)
+cudaError_t launch_filter3_bytes(int filter, const ImageSet& s, cudaStream_t st);
+
+}  // namespace b2d
+
+namespace b2d {
+// median 5/7, bilateral (uint8 in -> uint8 out, already noised)
+int run_denoise_pass(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, uint8_t* ws, cudaStream_t st);
+// quant / bloom: pixel-granular corruption written as a uint8 image
+int run_pixel_noise(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, uint8_t* ws, const b2d_fields* fields,
+                    uint64_t seed, uint64_t first_global, cudaStream_t st);
+// noise (operator `kind`, float where the reference keeps float) -> BayesShrink wavelet -> ->u8
+int run_wavelet(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, int kind, int mode, const NoiseArgs& na,
+                uint8_t* ws, cudaStream_t st);
+}  // namespace b2d

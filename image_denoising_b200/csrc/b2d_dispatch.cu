@@ -1,0 +1,252 @@
+// b2d_dispatch.cu - one batch -> kernel launches (b2d_run, b2d_run_host,
+// b2d_noise_field).  Replaces the closure dispatch of lib/model/test.py:1612-1784.
+#include "b2d_kernels.cuh"
+#include "b2d_prepass.cuh"
+#include "b2d_denoise.cuh"
+#include "b2d_plan.h"
+
+#include <algorithm>
+#include <cmath>
+
+using namespace b2d;
+
+#define CK(x)                                          \
+  do {                                                 \
+    cudaError_t e__ = (x);                             \
+    if (e__ != cudaSuccess) return fail_cuda(e__, #x); \
+  } while (0)
+
+// ---------------------------------------------------------------------------
+// dispatch
+// ---------------------------------------------------------------------------
+namespace {
+
+struct RunCtx {
+  b2d_plan* p;
+  const uint8_t* in;     // batch base
+  uint8_t* out;          // batch base
+  uint8_t* ws;
+  const b2d_fields* fields;
+  uint64_t seed, first_global;
+  cudaStream_t st;
+};
+
+ImageSet make_set(const b2d_plan* p, const uint8_t* in, uint8_t* out, const SpecGroup& g, int lo, int hi) {
+  ImageSet s;
+  s.in = in; s.out = out; s.h = p->h; s.w = p->w; s.rowbytes = p->rowbytes; s.elems = p->elems;
+  s.count = hi - lo;
+  s.first = g.images[lo];
+  s.list = g.contiguous ? nullptr : g.d_list + lo;
+  return s;
+}
+
+bool word_aligned(const b2d_plan* p, const void* a, const void* b) {
+  return p->rowbytes % 4 == 0 && ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b)) & 3u) == 0;
+}
+
+int filter3_kind(const b2d_spec& sp) {
+  if (sp.denoise == B2D_DENOISE_GAUS_BLUR) return FK_GAUS3;
+  if (sp.denoise == B2D_DENOISE_MEAN) return FK_MEAN3;
+  if (sp.denoise == B2D_DENOISE_MEDIAN && sp.ksize == 3) return FK_MEDIAN3;
+  return FK_NONE;
+}
+
+// denoise a uint8 image set that is already noised (src -> dst)
+int denoise_u8(const RunCtx& c, const b2d_spec& sp, const ImageSet& s) {
+  const int f3 = filter3_kind(sp);
+  if (f3 != FK_NONE) {
+    NoiseArgs none{};
+    none.elems = c.p->elems;
+    if (word_aligned(c.p, s.in, s.out)) CK(launch_fused3(NK_NONE, f3, s, none, c.st));
+    else CK(launch_filter3_bytes(f3, s, c.st));
+    return B2D_OK;
+  }
+  return run_denoise_pass(*c.p, sp, s, c.ws, c.st);
+}
+
+int run_group(const RunCtx& c, const SpecGroup& g, int lo, int hi) {
+  b2d_plan* p = c.p;
+  const b2d_spec& sp = g.spec;
+  const bool inject = c.fields != nullptr && c.fields->f0 != nullptr;
+  uint8_t* stage = c.ws + p->off_stage;
+  ImageSet s = make_set(p, c.in, c.out, g, lo, hi);
+
+  NoiseArgs na{};
+  na.k0 = (uint32_t)c.seed; na.k1 = (uint32_t)(c.seed >> 32);
+  na.first_global = c.first_global;
+  na.elems = p->elems;
+  if (inject) { na.f0 = c.fields->f0; na.f1 = c.fields->f1; }
+  int kind = NK_NONE;
+  switch (sp.noise) {
+    case B2D_NOISE_NONE: kind = NK_NONE; break;
+    case B2D_NOISE_GAUSSIAN: kind = NK_GAUSSIAN; na.p0 = (float)std::sqrt(sp.level); break;
+    case B2D_NOISE_SPECKLE: kind = NK_SPECKLE; na.p0 = (float)std::sqrt(sp.level); break;
+    case B2D_NOISE_SAP:
+      kind = NK_SAP; na.d0 = sp.level;
+      na.u0 = (uint32_t)std::max(0.0, std::min(32768.0, std::ceil(sp.level * 32768.0 - 0.5)));
+      if (inject && !na.f1) return fail(B2D_ERR_INVALID, "sap with injected fields needs f0 (u1) and f1 (u2)");
+      break;
+    case B2D_NOISE_UNIFORM: kind = NK_UNIFORM; na.p0 = (float)sp.level; break;
+    case B2D_NOISE_RAYLEIGH: kind = NK_RAYLEIGH; na.p0 = (float)sp.level; break;
+    case B2D_NOISE_GAMMA: kind = NK_GAMMA; na.p0 = (float)sp.level; break;
+    case B2D_NOISE_SHADER: kind = NK_SHADER; na.u0 = (sp.compat_flags & B2D_COMPAT_SHADER_BGR) ? 1u : 0u; break;
+    case B2D_NOISE_POISSON: {
+      kind = NK_POISSON;
+      float* par = reinterpret_cast<float*>(c.ws + p->off_par);
+      CK(launch_poisson_vals(s, reinterpret_cast<uint32_t*>(c.ws + p->off_bitmap), par, p->n, c.st));
+      na.img_par = par;
+      break;
+    }
+    case B2D_NOISE_PERIODIC: {
+      kind = NK_TABLE_ADD;
+      for (const PeriodicTable& t : p->periodic)
+        if (t.level == sp.level) na.tab = t.d_tab;
+      na.tab_stride = 0;
+      break;
+    }
+    case B2D_NOISE_BROWNIAN: {
+      kind = NK_TABLE_ADD;
+      BrownianArgs ba;
+      ba.sqrt_dt = std::sqrt(sp.level);
+      ba.chunk_sums = reinterpret_cast<double*>(c.ws + p->off_scan);
+      ba.nchunks = p->brown_chunks;
+      ba.field = c.ws + p->off_aux;
+      CK(launch_brownian_field(s, na, ba, inject, c.st));
+      na.tab = ba.field;
+      na.tab_stride = p->elems;
+      break;
+    }
+    case B2D_NOISE_QUANT:
+    case B2D_NOISE_BLOOM: {
+      // pixel-granular pre-pass writes the corrupted uint8 image; the denoiser then reads it
+      uint8_t* dst = sp.denoise == B2D_DENOISE_NONE ? c.out : stage;
+      ImageSet ps = s;
+      ps.out = dst;
+      const int rc = run_pixel_noise(*p, sp, ps, c.ws, c.fields, c.seed, c.first_global, c.st);
+      if (rc) return rc;
+      if (sp.denoise == B2D_DENOISE_NONE) return B2D_OK;
+      ImageSet ds = s;
+      ds.in = stage;
+      return denoise_u8(c, sp, ds);
+    }
+    default: return fail(B2D_ERR_INVALID, "unknown noise %d", sp.noise);
+  }
+  // brownian/periodic consume injected fields in their pre-pass, not in the operator
+  const bool op_inject = inject && kind != NK_TABLE_ADD && kind != NK_NONE && kind != NK_SHADER;
+  const int mode = op_inject ? NM_INJECT : NM_GEN;
+
+  if (sp.denoise == B2D_DENOISE_NONE) {
+    CK(launch_noise_only(kind, mode, s, na, c.st));
+    return B2D_OK;
+  }
+  if (sp.denoise == B2D_DENOISE_WAVELET) return run_wavelet(*p, sp, s, kind, mode, na, c.ws, c.st);
+  const int f3 = filter3_kind(sp);
+  if (f3 != FK_NONE && !op_inject && word_aligned(p, s.in, s.out)) {
+    CK(launch_fused3(kind, f3, s, na, c.st));          // the one-pass hot path
+    return B2D_OK;
+  }
+  // two-pass: noise -> stage (uint8) -> denoiser
+  ImageSet ns = s;
+  ns.out = stage;
+  CK(launch_noise_only(kind, mode, ns, na, c.st));
+  ImageSet ds = s;
+  ds.in = stage;
+  return denoise_u8(c, sp, ds);
+}
+
+int run_range(const RunCtx& c, int img0, int cnt) {
+  for (const SpecGroup& g : c.p->groups) {
+    const int lo = (int)(std::lower_bound(g.images.begin(), g.images.end(), img0) - g.images.begin());
+    const int hi = (int)(std::lower_bound(g.images.begin(), g.images.end(), img0 + cnt) - g.images.begin());
+    if (hi <= lo) continue;
+    const int rc = run_group(c, g, lo, hi);
+    if (rc) return rc;
+  }
+  return B2D_OK;
+}
+
+}  // namespace
+
+extern "C" int b2d_run(b2d_plan* plan, const uint8_t* d_in, uint8_t* d_out, void* d_ws,
+                       const b2d_fields* fields, uint64_t seed, uint64_t first_global_image_index,
+                       void* cuda_stream) {
+  if (!plan) return fail(B2D_ERR_INVALID, "b2d_run: null plan");
+  if (plan->n == 0) return B2D_OK;
+  if (!d_in || !d_out) return fail(B2D_ERR_INVALID, "b2d_run: null image buffer");
+  if (!d_ws && plan->ws_bytes) return fail(B2D_ERR_INVALID, "b2d_run: workspace of %zu bytes required", plan->ws_bytes);
+  CK(cudaSetDevice(plan->device));
+  RunCtx c{plan, d_in, d_out, static_cast<uint8_t*>(d_ws), fields, seed, first_global_image_index,
+           static_cast<cudaStream_t>(cuda_stream)};
+  return run_range(c, 0, plan->n);
+}
+
+// ---------------------------------------------------------------------------
+// host-buffer entry point: chunked H2D / kernels / D2H on three streams
+// ---------------------------------------------------------------------------
+extern "C" int b2d_run_host(b2d_plan* plan, const uint8_t* h_in, uint8_t* h_out, uint64_t seed,
+                            uint64_t first_global_image_index) {
+  if (!plan) return fail(B2D_ERR_INVALID, "b2d_run_host: null plan");
+  if (plan->n == 0) return B2D_OK;
+  if (!h_in || !h_out) return fail(B2D_ERR_INVALID, "b2d_run_host: null image buffer");
+  CK(cudaSetDevice(plan->device));
+  const size_t bytes = (size_t)plan->elems * plan->n;
+  if (!plan->h_ready) {
+    CK(cudaMalloc(&plan->h_d_in, bytes));
+    CK(cudaMalloc(&plan->h_d_out, bytes));
+    if (plan->ws_bytes) CK(cudaMalloc(&plan->h_d_ws, plan->ws_bytes));
+    for (int i = 0; i < 3; ++i) CK(cudaStreamCreateWithFlags(&plan->h_streams[i], cudaStreamNonBlocking));
+    plan->h_ready = true;
+  }
+  // chunks of >= 32 MiB (at least one image) so each copy runs at full PCIe rate
+  int per = (int)std::max<uint64_t>(1, (32ull << 20) / plan->elems);
+  if (plan->need_aux) per = plan->n;  // pre-pass workspaces are batch-indexed but shared: keep one chunk
+  int k = 0;
+  for (int img0 = 0; img0 < plan->n; img0 += per, ++k) {
+    const int cnt = std::min(per, plan->n - img0);
+    cudaStream_t st = plan->h_streams[k % 3];
+    const size_t off = (size_t)img0 * plan->elems, len = (size_t)cnt * plan->elems;
+    CK(cudaMemcpyAsync(plan->h_d_in + off, h_in + off, len, cudaMemcpyHostToDevice, st));
+    RunCtx c{plan, plan->h_d_in, plan->h_d_out, plan->h_d_ws, nullptr, seed, first_global_image_index, st};
+    const int rc = run_range(c, img0, cnt);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(h_out + off, plan->h_d_out + off, len, cudaMemcpyDeviceToHost, st));
+  }
+  for (int i = 0; i < 3; ++i) CK(cudaStreamSynchronize(plan->h_streams[i]));
+  return B2D_OK;
+}
+
+// ---------------------------------------------------------------------------
+// test hook: dump the generator's noise fields
+// ---------------------------------------------------------------------------
+extern "C" int b2d_noise_field(b2d_plan* plan, float* d_f0, float* d_f1, uint64_t seed,
+                               uint64_t first_global_image_index, void* cuda_stream) {
+  if (!plan || !d_f0) return fail(B2D_ERR_INVALID, "b2d_noise_field: null argument");
+  CK(cudaSetDevice(plan->device));
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  for (const SpecGroup& g : plan->groups) {
+    const b2d_spec& sp = g.spec;
+    NoiseArgs na{};
+    na.k0 = (uint32_t)seed; na.k1 = (uint32_t)(seed >> 32);
+    na.first_global = first_global_image_index;
+    na.elems = plan->elems;
+    na.dump0 = d_f0; na.dump1 = d_f1;
+    int kind;
+    switch (sp.noise) {
+      case B2D_NOISE_GAUSSIAN: kind = NK_GAUSSIAN; na.p0 = (float)std::sqrt(sp.level); break;
+      case B2D_NOISE_SPECKLE: kind = NK_SPECKLE; na.p0 = (float)std::sqrt(sp.level); break;
+      case B2D_NOISE_SAP:
+        kind = NK_SAP;
+        na.u0 = (uint32_t)std::max(0.0, std::min(32768.0, std::ceil(sp.level * 32768.0 - 0.5)));
+        if (!d_f1) return fail(B2D_ERR_INVALID, "b2d_noise_field: sap needs d_f1");
+        break;
+      case B2D_NOISE_UNIFORM: kind = NK_UNIFORM; na.p0 = (float)sp.level; break;
+      case B2D_NOISE_RAYLEIGH: kind = NK_RAYLEIGH; na.p0 = (float)sp.level; break;
+      case B2D_NOISE_GAMMA: kind = NK_GAMMA; na.p0 = (float)sp.level; break;
+      default: return fail(B2D_ERR_UNSUPPORTED, "b2d_noise_field: noise %d has no dumpable field", sp.noise);
+    }
+    // the operators never read pixels in dump mode except poisson (not dumpable): `in` may be any valid buffer
+    ImageSet s = make_set(plan, reinterpret_cast<const uint8_t*>(d_f0), nullptr, g, 0, (int)g.images.size());
+    CK(launch_noise_only(kind, NM_DUMP, s, na, st));
+  }
+  return B2D_OK;
+}

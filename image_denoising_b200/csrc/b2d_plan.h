@@ -1,0 +1,40 @@
+// b2d_plan.h - host-side plan object behind the opaque b2d_plan handle.
+#pragma once
+#include "../../include/b200denoise.h"
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <vector>
+
+namespace b2d {
+
+int fail(int code, const char* fmt, ...);
+int fail_cuda(cudaError_t e, const char* what);
+
+struct SpecGroup {
+  b2d_spec spec;
+  std::vector<int> images;   // ascending batch indices
+  bool contiguous;           // images == [first, first + count)
+  int* d_list;               // device copy of `images` when !contiguous
+};
+
+struct PeriodicTable {
+  double level;              // pi, 100 or B2D_LEVEL_SIZE
+  uint8_t* d_tab;            // elems bytes
+};
+
+}  // namespace b2d
+
+struct b2d_plan {
+  int device, n, h, w, rowbytes;
+  uint64_t elems;
+  std::vector<b2d::SpecGroup> groups;
+  std::vector<b2d::PeriodicTable> periodic;
+  // workspace layout (byte offsets into the caller's d_ws)
+  size_t ws_bytes, off_par, off_bitmap, off_stage, off_aux, off_scan;
+  uint32_t brown_chunks;
+  bool need_aux;
+  // b2d_run_host resources (lazily created)
+  uint8_t *h_d_in, *h_d_out, *h_d_ws;
+  cudaStream_t h_streams[3];
+  bool h_ready;
+};

@@ -1,0 +1,192 @@
+// b2d_prepass.cu - small per-image pre-passes that produce parameters / u8
+// noise fields consumed by the fused kernels.
+//   poisson : vals = 2^ceil(log2(#unique values))         (skimage random_noise)
+//   periodic: (sin(linspace(-L, L, n)) * 255) ->u8         (minibatch.py:1042-1045)
+//   brownian: B = [0, cumsum(sqrt(dt) z)], (B * 255) ->u8  (minibatch.py:822-827)
+#include "b2d_kernels.cuh"
+#include "b2d_prepass.cuh"
+
+namespace b2d {
+
+// ---------------------------------------------------------------- poisson --
+__global__ void __launch_bounds__(256) k_unique_bitmap(ImageSet s, uint32_t* bitmaps /* [n][8] */) {
+  __shared__ uint32_t bm[8];
+  if (threadIdx.x < 8) bm[threadIdx.x] = 0u;
+  __syncthreads();
+  const int img_local = image_of(s, blockIdx.z);
+  const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
+  for (uint64_t e = (uint64_t)blockIdx.x * 256 + threadIdx.x; e < s.elems; e += (uint64_t)gridDim.x * 256) {
+    const uint32_t b = __ldg(img + e);
+    const uint32_t bit = 1u << (b & 31u);
+    if (!(bm[b >> 5] & bit)) atomicOr(&bm[b >> 5], bit);
+  }
+  __syncthreads();
+  if (threadIdx.x < 8 && bm[threadIdx.x]) atomicOr(&bitmaps[img_local * 8 + threadIdx.x], bm[threadIdx.x]);
+}
+
+__global__ void k_poisson_vals(const uint32_t* bitmaps, float* vals, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int cnt = 0;
+  for (int k = 0; k < 8; ++k) cnt += __popc(bitmaps[i * 8 + k]);
+  int p = 1;
+  while (p < cnt) p <<= 1;          // 2 ** ceil(log2(cnt))
+  vals[i] = (float)p;
+}
+
+cudaError_t launch_poisson_vals(const ImageSet& s, uint32_t* bitmaps, float* vals, int n_batch, cudaStream_t st) {
+  cudaError_t e = cudaMemsetAsync(bitmaps, 0, sizeof(uint32_t) * 8 * n_batch, st);
+  if (e != cudaSuccess) return e;
+  uint32_t bx = (uint32_t)((s.elems + 256 * 64 - 1) / (256 * 64));
+  if (bx < 1) bx = 1;
+  k_unique_bitmap<<<dim3(bx, 1, s.count), 256, 0, st>>>(s, bitmaps);
+  count_launch();
+  k_poisson_vals<<<(n_batch + 127) / 128, 128, 0, st>>>(bitmaps, vals, n_batch);
+  count_launch();
+  return cudaGetLastError();
+}
+
+// --------------------------------------------------------------- periodic --
+__global__ void __launch_bounds__(256) k_periodic_table(uint8_t* tab, uint64_t n, double start, double stop,
+                                                        double step) {
+  for (uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (uint64_t)gridDim.x * 256) {
+    // np.linspace: y = arange(n) * step + start (two roundings); y[-1] = stop
+    double t = __dadd_rn(__dmul_rn((double)i, step), start);
+    if (i == n - 1 && n > 1) t = stop;
+    tab[i] = (uint8_t)wrap_u8(__dmul_rn(sin(t), 255.0));
+  }
+}
+
+cudaError_t launch_periodic_table(uint8_t* tab, uint64_t n, double lim, cudaStream_t st) {
+  const double start = -lim, stop = lim;
+  const double step = n > 1 ? (stop - start) / (double)(n - 1) : 0.0;
+  uint32_t bx = (uint32_t)((n + 255) / 256);
+  if (bx > 148u * 16u) bx = 148u * 16u;
+  k_periodic_table<<<bx, 256, 0, st>>>(tab, n, start, stop, step);
+  count_launch();
+  return cudaGetLastError();
+}
+
+// --------------------------------------------------------------- brownian --
+// dB[j] = sqrt(dt) * z[j], j in [0, n-1); B[i] = sum_{j<i} dB[j].  One thread
+// per 8-element group, BR_CHUNK elements per CTA, float64 throughout.
+constexpr int BR_THREADS = 256;
+constexpr int BR_CHUNK = BR_THREADS * 8;
+
+template <bool INJECT>
+__device__ __forceinline__ void brownian_steps(const NoiseArgs& na, const BrownianArgs& ba, int img_local,
+                                               uint32_t g, double (&d)[8]) {
+  const uint64_t nz = na.elems - 1;
+  if (INJECT) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const uint64_t j = (uint64_t)g * 8u + i;
+      d[i] = j < nz ? __dmul_rn(ba.sqrt_dt, na.f0[(uint64_t)img_local * nz + j]) : 0.0;
+    }
+  } else {
+    GroupCtx gc{(uint32_t)img_local, g, nullptr};
+    const uint4 r = group_random(na, gc, 0);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      float z0, z1;
+      box_muller16(r16(r, 2 * k), r16(r, 2 * k + 1), z0, z1);
+      const uint64_t j = (uint64_t)g * 8u + 2 * k;
+      d[2 * k] = j < nz ? __dmul_rn(ba.sqrt_dt, (double)z0) : 0.0;
+      d[2 * k + 1] = j + 1 < nz ? __dmul_rn(ba.sqrt_dt, (double)z1) : 0.0;
+    }
+  }
+}
+
+__device__ __forceinline__ double block_exclusive_scan(double x, double* total) {
+  __shared__ double warp_sum[BR_THREADS / 32];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  double inc = x;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const double y = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += y;
+  }
+  if (lane == 31) warp_sum[wid] = inc;
+  __syncthreads();
+  double base = 0.0, tot = 0.0;
+#pragma unroll
+  for (int k = 0; k < BR_THREADS / 32; ++k) {
+    if (k < wid) base += warp_sum[k];
+    tot += warp_sum[k];
+  }
+  __syncthreads();
+  *total = tot;
+  return base + inc - x;
+}
+
+template <bool INJECT>
+__global__ void __launch_bounds__(BR_THREADS) k_brown_chunksum(ImageSet s, NoiseArgs na, BrownianArgs ba) {
+  const int img_local = image_of(s, blockIdx.z);
+  const uint32_t g = blockIdx.x * BR_THREADS + threadIdx.x;
+  double d[8], sum = 0.0;
+  brownian_steps<INJECT>(na, ba, img_local, g, d);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) sum += d[i];
+  double total;
+  block_exclusive_scan(sum, &total);
+  if (threadIdx.x == 0) ba.chunk_sums[(uint64_t)img_local * ba.nchunks + blockIdx.x] = total;
+}
+
+// exclusive scan of one image's chunk sums, in place (serial per image: <= a few thousand terms)
+__global__ void k_brown_scan(ImageSet s, BrownianArgs ba) {
+  const int z = blockIdx.x * blockDim.x + threadIdx.x;
+  if (z >= s.count) return;
+  double* cs = ba.chunk_sums + (uint64_t)image_of(s, z) * ba.nchunks;
+  double run = 0.0;
+  for (uint32_t k = 0; k < ba.nchunks; ++k) {
+    const double t = cs[k];
+    cs[k] = run;
+    run += t;
+  }
+}
+
+template <bool INJECT>
+__global__ void __launch_bounds__(BR_THREADS) k_brown_field(ImageSet s, NoiseArgs na, BrownianArgs ba) {
+  const int img_local = image_of(s, blockIdx.z);
+  const uint32_t g = blockIdx.x * BR_THREADS + threadIdx.x;
+  double d[8], sum = 0.0;
+  brownian_steps<INJECT>(na, ba, img_local, g, d);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) sum += d[i];
+  double total;
+  double b = block_exclusive_scan(sum, &total) + ba.chunk_sums[(uint64_t)img_local * ba.nchunks + blockIdx.x];
+  uint8_t* f = ba.field + (uint64_t)img_local * na.elems;
+  uint32_t v[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    v[i] = wrap_u8(__dmul_rn(b, 255.0));   // B[8g + i]
+    b += d[i];
+  }
+  const uint64_t e = (uint64_t)g * 8u;
+  if (e + 8u <= na.elems && ((reinterpret_cast<uintptr_t>(f + e) & 7u) == 0)) {
+    *reinterpret_cast<uint2*>(f + e) = make_uint2(pack4(v[0], v[1], v[2], v[3]), pack4(v[4], v[5], v[6], v[7]));
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      if (e + i < na.elems) f[e + i] = (uint8_t)v[i];
+  }
+}
+
+cudaError_t launch_brownian_field(const ImageSet& s, const NoiseArgs& na, const BrownianArgs& ba, bool inject,
+                                  cudaStream_t st) {
+  if (s.count <= 0) return cudaSuccess;
+  const dim3 grid(ba.nchunks, 1, s.count);
+  if (inject) k_brown_chunksum<true><<<grid, BR_THREADS, 0, st>>>(s, na, ba);
+  else k_brown_chunksum<false><<<grid, BR_THREADS, 0, st>>>(s, na, ba);
+  count_launch();
+  k_brown_scan<<<(s.count + 63) / 64, 64, 0, st>>>(s, ba);
+  count_launch();
+  if (inject) k_brown_field<true><<<grid, BR_THREADS, 0, st>>>(s, na, ba);
+  else k_brown_field<false><<<grid, BR_THREADS, 0, st>>>(s, na, ba);
+  count_launch();
+  return cudaGetLastError();
+}
+
+uint32_t brownian_chunks(uint64_t elems) { return (uint32_t)((elems + BR_CHUNK - 1) / BR_CHUNK); }
+
+}  // namespace b2d

@@ -1,0 +1,20 @@
+// b2d_prepass.cuh - declarations for the per-image pre-passes.
+#pragma once
+#include "b2d_kernels.cuh"
+
+namespace b2d {
+
+struct BrownianArgs {
+  double sqrt_dt;
+  double* chunk_sums;   // [batch][nchunks] workspace
+  uint32_t nchunks;
+  uint8_t* field;       // [batch][elems] u8 noise field (batch-indexed)
+};
+
+uint32_t brownian_chunks(uint64_t elems);
+cudaError_t launch_poisson_vals(const ImageSet& s, uint32_t* bitmaps, float* vals, int n_batch, cudaStream_t st);
+cudaError_t launch_periodic_table(uint8_t* tab, uint64_t n, double lim, cudaStream_t st);
+cudaError_t launch_brownian_field(const ImageSet& s, const NoiseArgs& na, const BrownianArgs& ba, bool inject,
+                                  cudaStream_t st);
+
+}  // namespace b2d

@@ -1,0 +1,167 @@
+/* b200denoise.h - C ABI of libb200denoise.so
+ *
+ * B200 (sm_100a) implementation of the image-corruption + denoising
+ * preprocessing path of mahesh-kashyap-ml/image-denoising.  The reference has
+ * no FFI for this path: it is a set of Python closures
+ *   add_<noise>_noise(spec)   lib/roi_data_layer/minibatch.py:87-1516
+ *                             lib/model/test.py:193-1607
+ * selected by substring tests on the `--noise` spec string
+ *   (minibatch.py:1518-1673, test.py:1612-1831).
+ * Each entry point below names the reference expression it replaces.  Plain
+ * pointers and sizes only; no C++/torch types cross this boundary.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative b2d_status; nothing
+ *     throws or aborts across the ABI; b2d_last_error() gives the message of
+ *     the last failure on the calling thread;
+ *   - the caller owns all device buffers (input, output, workspace, fields);
+ *     the library allocates only inside b2d_plan_create / b2d_run_host and
+ *     frees in b2d_plan_destroy;
+ *   - b2d_run is asynchronous on the caller's CUDA stream;
+ *   - images are N x H x W x 3 uint8, interleaved BGR, C-contiguous (the
+ *     layout cv2.imread gives the reference, minibatch.py:85);
+ *   - randomness is Philox4x32-10 keyed by (seed) with counter
+ *     (element group, substream, global image index): results do not depend on
+ *     batch split, launch geometry or GPU count.  There is no global RNG.
+ */
+#ifndef B200DENOISE_H
+#define B200DENOISE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  B2D_OK = 0,
+  B2D_ERR_INVALID = -1,     /* bad argument                                  */
+  B2D_ERR_UNSUPPORTED = -2, /* valid request this build cannot run           */
+  B2D_ERR_CUDA = -3,        /* CUDA runtime error (message has the detail)   */
+  B2D_ERR_PARSE = -4,       /* spec string not understood / unknown level    */
+  B2D_ERR_NO_DEVICE = -5    /* no CUDA device: there is NO CPU fallback      */
+} b2d_status;
+
+/* order = the reference's top-level elif chain, minibatch.py:1575-1634 */
+typedef enum {
+  B2D_NOISE_NONE = 0,   /* retain_original, minibatch.py:1512-1516 */
+  B2D_NOISE_GAUSSIAN,   /* add_gaussian_noise  minibatch.py:87-201   */
+  B2D_NOISE_POISSON,    /* add_poisson_noise   minibatch.py:203-251  */
+  B2D_NOISE_SAP,        /* add_sap_noise       minibatch.py:253-372  */
+  B2D_NOISE_SPECKLE,    /* add_speckle_noise   minibatch.py:374-490  */
+  B2D_NOISE_PERIODIC,   /* add_periodic_noise  minibatch.py:1034-1206 */
+  B2D_NOISE_BROWNIAN,   /* add_brownian_noise  minibatch.py:809-1032 */
+  B2D_NOISE_QUANT,      /* add_quant_noise     minibatch.py:492-667  */
+  B2D_NOISE_UNIFORM,    /* add_uniform_noise   minibatch.py:669-807  */
+  B2D_NOISE_GAMMA,      /* add_gamma_noise     minibatch.py:1208-1347 */
+  B2D_NOISE_RAYLEIGH,   /* add_rayleigh_noise  minibatch.py:1349-1484 */
+  B2D_NOISE_BLOOM,      /* add_bloom -> Automold.add_sun_flare, minibatch.py:1485-1489 */
+  B2D_NOISE_SHADER,     /* add_shader (PIL Brightness x3), minibatch.py:1505-1511 */
+  B2D_NOISE_COUNT
+} b2d_noise;
+
+typedef enum {
+  B2D_DENOISE_NONE = 0,
+  B2D_DENOISE_GAUS_BLUR, /* cv2.GaussianBlur(u8,(3,3),0)      minibatch.py:119 */
+  B2D_DENOISE_MEAN,      /* cv2.blur(u8,(3,3))                minibatch.py:136 */
+  B2D_DENOISE_MEDIAN,    /* cv2.medianBlur(u8,k) k=3 (5,7)    minibatch.py:153 */
+  B2D_DENOISE_BILATERAL, /* cv2.bilateralFilter(u8,9,20,100,BORDER_CONSTANT) minibatch.py:172 */
+  B2D_DENOISE_WAVELET,   /* skimage denoise_wavelet BayesShrink soft YCbCr  minibatch.py:92-96 */
+  B2D_DENOISE_COUNT
+} b2d_denoise;
+
+enum { B2D_WAVELET_DB1 = 0, B2D_WAVELET_BIOR15 = 1 };
+
+/* compat_flags */
+enum {
+  B2D_COMPAT_SHADER_BGR = 1, /* keep BGR order for `shader` (reference returns RGB, quirk Q5) */
+  B2D_COMPAT_SAP_SVP06 = 2   /* salt_vs_pepper 0.6 (training noise-only sap 0.8, minibatch.py:367) */
+};
+
+/* B2D_LEVEL_SIZE: periodic `varsize` (L = H*W*3, minibatch.py:1066) */
+#define B2D_LEVEL_SIZE (-1.0)
+
+typedef struct b2d_spec {
+  int32_t noise;        /* b2d_noise                                             */
+  int32_t denoise;      /* b2d_denoise                                           */
+  double level;         /* var / amount / k / high / dt / L / scale (README.md:90-100) */
+  int32_t ksize;        /* median window 3|5|7 (gaus_blur/mean are fixed 3)      */
+  int32_t d;            /* bilateral diameter (9)                                */
+  float sigma_color;    /* bilateral (20)                                        */
+  float sigma_space;    /* bilateral (100)                                       */
+  int32_t wavelet;      /* B2D_WAVELET_*                                         */
+  int32_t levels;       /* wavelet levels, 0 = skimage's automatic choice        */
+  int32_t compat_flags;
+  int32_t reserved;
+} b2d_spec;
+
+/* Optional injected noise fields (DEVICE pointers, float64, one value per
+ * uint8 element, N*H*W*3 each unless noted) so that the CUDA path and the CPU
+ * oracle consume identical randomness.  Meaning by noise:
+ *   gaussian/speckle f0 = n (already scaled by sqrt(var))  rayleigh/gamma/uniform f0 = samples
+ *   sap       f0 = u1, f1 = u2                             poisson  f0 = k (integer draws)
+ *   brownian  f0 = z, N*(H*W*3-1) standard normals         quant    f0 = centres, N*k*3 (Lab)
+ *   bloom     f0 = N*8*7 doubles (alpha,cx,cy,radius,c0,c1,c2 per circle)            */
+typedef struct b2d_fields {
+  const double* f0;
+  const double* f1;
+} b2d_fields;
+
+typedef struct b2d_plan b2d_plan; /* opaque */
+
+/* Parse a reference `--noise` spec string (tools/test_net.py:47-49,
+ * tools/trainval_net.py:52-54) with the substring precedence of the closures
+ * (minibatch.py:89-199 and twins).  `mix`/`curvelet` specs are host-side
+ * policy (random.choice over a list) and are rejected here with
+ * B2D_ERR_UNSUPPORTED: the Python front-end resolves them to a concrete spec. */
+int b2d_parse_spec(const char* spec, b2d_spec* out);
+
+/* A plan fixes (device, N, H, W) and one spec per image (n_specs == N) or one
+ * spec for the whole batch (n_specs == 1).  Replaces the per-image closure
+ * definition + dispatch of test.py:189-1784. */
+int b2d_plan_create(b2d_plan** out, int device, int n, int h, int w,
+                    const b2d_spec* specs, int n_specs);
+int b2d_plan_workspace_bytes(const b2d_plan* plan, size_t* bytes);
+void b2d_plan_destroy(b2d_plan* plan);
+
+/* corrupt + denoise the whole batch:  d_out[i] = closure(spec_i)(d_in[i]).
+ * d_ws: workspace of b2d_plan_workspace_bytes bytes (may be NULL when 0).
+ * Image i of the batch uses Philox counter `first_global_image_index + i`. */
+int b2d_run(b2d_plan* plan, const uint8_t* d_in, uint8_t* d_out, void* d_ws,
+            const b2d_fields* fields_or_null, uint64_t seed,
+            uint64_t first_global_image_index, void* cuda_stream);
+
+/* Same call with HOST buffers (what `im = add_<noise>_noise(spec)` is for a
+ * NumPy caller): chunked H2D copy, kernels and D2H copy pipelined on internal
+ * streams with internal device buffers; returns after h_out is complete.
+ * Pinned host memory (b2d_host_register) is needed for the copies to overlap. */
+int b2d_run_host(b2d_plan* plan, const uint8_t* h_in, uint8_t* h_out,
+                 uint64_t seed, uint64_t first_global_image_index);
+int b2d_host_register(void* ptr, size_t bytes);
+int b2d_host_unregister(void* ptr);
+
+/* Test hook: write the noise field(s) the generator produces for this plan's
+ * noise (float32, N*H*W*3 each; f1 only for sap) in the form the oracle's
+ * `fields=` argument consumes, WITHOUT touching the image. */
+int b2d_noise_field(b2d_plan* plan, float* d_f0, float* d_f1, uint64_t seed,
+                    uint64_t first_global_image_index, void* cuda_stream);
+
+/* Per-image result statistics gathered after the run (8(e): the only data
+ * that ever crosses GPUs): checksum = sum of bytes * (1 + index mod 251)
+ * mod 2^64 of d_out[i]; sse = sum (d_out - d_ref)^2 (for PSNR vs clean). */
+int b2d_stats(b2d_plan* plan, const uint8_t* d_ref, const uint8_t* d_out,
+              uint64_t* d_checksum, double* d_sse, void* cuda_stream);
+
+/* number of kernel launches issued by this library on the calling thread
+ * since the last b2d_reset_launch_count() (bench.py's gpu_launches) */
+uint64_t b2d_launch_count(void);
+void b2d_reset_launch_count(void);
+
+const char* b2d_last_error(void);
+const char* b2d_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DENOISE_H */
