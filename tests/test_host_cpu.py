@@ -1,0 +1,104 @@
+"""CPU: host logic - the spec grammar, the C parser, the library's export list."""
+import ctypes
+import os
+import random
+import re
+
+import pytest
+
+from image_denoising_b200 import _lib, spec
+from oracle import closures as C
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+NOISES = ["gaussian", "poisson", "sap", "speckle", "periodic", "brownian", "quant", "uniform", "gamma", "rayleigh",
+          "bloom", "shader", "original"]
+DENS = ["", "_wavelet", "_gaus_blur", "_mean", "_median", "_bilateral"]
+
+
+def all_specs():
+    for n in NOISES:
+        for d in DENS:
+            for tag, _ in spec.LEVELS.get(n, [("", 0)]):
+                yield n + d + ("_var" + tag if tag else "")
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    L = _lib.lib()
+    header = open(os.path.join(ROOT, "include", "b200denoise.h")).read()
+    declared = set(re.findall(r"\b(b2d_[a-z_]+)\s*\(", header))
+    assert declared == set(_lib.EXPORTS)
+    for name in declared:
+        assert hasattr(L, name), name
+    assert b"sm_100a" in L.b2d_version()
+    assert ctypes.sizeof(_lib.B2DSpec) == 48
+
+
+@pytest.mark.parametrize("s", list(all_specs()))
+def test_python_c_and_reference_ladder_agree(s):
+    L = _lib.lib()
+    cs = _lib.B2DSpec()
+    assert L.b2d_parse_spec(s.encode(), ctypes.byref(cs)) == 0
+    ps = spec.parse(s)
+    pc = ps.to_c()
+    assert (cs.noise, cs.denoise, cs.level, cs.ksize, cs.d, cs.wavelet, cs.levels) == \
+           (pc.noise, pc.denoise, pc.level, pc.ksize, pc.d, pc.wavelet, pc.levels)
+    noise, den, level = C.ladder(s)
+    assert ps.noise == (noise or "none")
+    if noise is not None:
+        assert ps.denoise == (den or "none")
+        if level is not None and level != "size" and noise != "periodic":
+            assert ps.level == float(level)
+
+
+def test_unknown_level_and_unsupported_specs():
+    L = _lib.lib()
+    cs = _lib.B2DSpec()
+    assert L.b2d_parse_spec(b"gaussian_median_var9", ctypes.byref(cs)) == _lib.ERR_PARSE
+    assert b"no known level" in L.b2d_last_error()
+    assert L.b2d_parse_spec(b"noise_mix_var_low", ctypes.byref(cs)) == _lib.ERR_UNSUPPORTED
+    assert L.b2d_parse_spec(b"curvelet", ctypes.byref(cs)) == _lib.ERR_UNSUPPORTED
+    with pytest.raises(spec.SpecError):
+        spec.parse("sap_mean_var0.5")
+    with pytest.raises(spec.SpecError):
+        spec.parse("noise_mix_var_low")
+
+
+def test_substring_precedence_quirks():
+    # 'var0.09' must not be read as 'var0.9'; 'var10' not as 'var1.0'; first noise name wins
+    assert spec.parse("brownian_var0.09").level == 0.09 and spec.parse("brownian_var0.009").level == 0.009
+    assert spec.parse("quant_var10").level == 10 and spec.parse("quant_median_var3").level == 3
+    assert spec.parse("periodic_varsize").level == _lib.LEVEL_SIZE
+    assert spec.parse("gaussian_poisson_var0.1").noise == "gaussian"
+    assert spec.parse("speckle_gaussian_var1.0").noise == "gaussian"       # chain order, not string order
+    assert spec.parse("sap_median_var0.4").denoise == "median"
+    assert spec.parse("sap_var0.4_median").denoise == "none"               # needs the literal 'sap_median'
+    assert spec.parse("original_median").denoise == "median"               # post-denoise pass on a clean image
+    assert spec.parse("gaussian_median_var1.0", ksize=7).ksize == 7
+
+
+def test_mix_resolution_uses_the_reference_lists():
+    for side in ("test", "train"):
+        lists = spec.MIX_LISTS[side]
+        assert len(lists["var_low"]) == len(lists["var_medium"]) == len(lists["var_high"]) == 13
+        for key, lst in lists.items():
+            for s in lst:
+                spec.parse(s)                                              # every entry is a valid concrete spec
+            got = {spec.resolve_mix("noise_mix_" + key, side, random.Random(i)) for i in range(400)}
+            assert got == set(lst)
+    assert len(spec.MIX_LISTS["test"]["var_all"]) == 42 and len(spec.MIX_LISTS["train"]["var_all"]) == 38
+    assert spec.MIX_LISTS["test"]["var_low"][9] == "quant_var3" and spec.MIX_LISTS["train"]["var_low"][9] == "quant_var10"
+    assert spec.resolve_mix("sap_mean_var0.4") == "sap_mean_var0.4"
+
+
+def test_plan_create_fails_loudly_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    L = _lib.lib()
+    cs = spec.parse("sap_mean_var0.4").to_c()
+    h = ctypes.c_void_p()
+    assert L.b2d_plan_create(ctypes.byref(h), 0, 1, 8, 8, ctypes.byref(cs), 1) == _lib.ERR_NO_DEVICE
+    assert b"no CPU fallback" in L.b2d_last_error()
+    from image_denoising_b200 import api
+    with pytest.raises(RuntimeError):
+        api.Plan(1, 8, 8, "sap_mean_var0.4")
