@@ -1,0 +1,294 @@
+#!/usr/bin/env python
+"""bench.py - headline benchmark of the corrupt -> denoise hot path.
+
+Metric (BASELINE.json): Mpixels/s per noise x denoise.  Workload at every N:
+BASELINE config C2 per GPU - a 512 x 600 x 1000 x 3 uint8 batch resident in
+HBM, one "step" = the two bandwidth-bound combinations named there
+(`sap_mean_var0.4` and `gaussian_gaus_blur_var1.5`) applied to the whole batch.
+Weak scaling: every rank owns its own 512 images (global image index =
+rank * 512 + i), no collective on the data path.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+One JSON line on stdout (rank 0).  `--impl reference` times the CPU oracle
+(the transcription of the reference's closures over cv2 / NumPy) on the host.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SPECS = ["sap_mean_var0.4", "gaussian_gaus_blur_var1.5"]
+N_IMAGES, H, W = 512, 600, 1000
+SEED = 3                                   # cfg.RNG_SEED (lib/model/config.py:255)
+ALGO_BYTES_PER_PIXEL = 6.0                 # 3 B read + 3 B written
+WORKLOAD = "C2: 512x600x1000 RGB uint8 per GPU; step = sap_mean_var0.4 + gaussian_gaus_blur_var1.5"
+
+
+def smooth_batch_torch(n, h, w, device, seed):
+    """SURVEY.md 8(d) `smooth` synthetic images, generated on the device."""
+    import torch
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    y = torch.arange(h, device=device, dtype=torch.float32).view(1, h, 1, 1)
+    x = torch.arange(w, device=device, dtype=torch.float32).view(1, 1, w, 1)
+    c = torch.arange(3, device=device, dtype=torch.float32).view(1, 1, 1, 3)
+    out = torch.empty((n, h, w, 3), dtype=torch.uint8, device=device)
+    step = 64
+    for i in range(0, n, step):
+        m = min(step, n - i)
+        ph = torch.rand((m, 1, 1, 1), generator=g, device=device) * 6.28
+        v = 127.5 + 60 * torch.cos(2 * np.pi * x / w * 3 + c + ph) + 60 * torch.cos(2 * np.pi * y / h * 2 + 2 * c)
+        v = v + 8 * torch.randn((m, h, w, 3), generator=g, device=device)
+        out[i:i + m] = v.clamp_(0, 255).to(torch.uint8)
+    return out
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([s.strip() for s in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i] == "Active"})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def _cpu_worker(args):
+    import cv2
+    cv2.setNumThreads(1)
+    from oracle import closures as C
+    spec, imgs, seed = args
+    rng = np.random.RandomState(seed)
+    return [C.corrupt(im, spec, rng=rng).shape[0] for im in imgs]
+
+
+def cpu_reference(images, specs, workers, repeats=1):
+    """The oracle (kind 'port': the reference's closures transcribed over the
+    same cv2 / NumPy calls) on `workers` host processes; returns Mpix/s."""
+    import multiprocessing as mp
+    n = len(images)
+    chunks = [images[i::workers] for i in range(workers) if len(images[i::workers])]
+    jobs = [(s, ch, SEED + k) for s in specs for k, ch in enumerate(chunks)]
+    best = None
+    with mp.get_context("fork").Pool(workers) as pool:
+        pool.map(_cpu_worker, [(specs[0], images[:1], 0)] * workers)       # warm the pool
+        for _ in range(repeats):
+            t0 = time.perf_counter()
+            pool.map(_cpu_worker, jobs, chunksize=1)
+            dt = time.perf_counter() - t0
+            best = dt if best is None else min(best, dt)
+    mpix = n * len(specs) * images[0].shape[0] * images[0].shape[1] / 1e6
+    return mpix / best, best
+
+
+def host_sample(n, seed):
+    """CPU-side sample of the same synthetic workload (SURVEY.md 8(d) `smooth`)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from conftest import synth_image
+    return [synth_image(H, W, seed + i, "smooth") for i in range(n)]
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    workers = os.cpu_count() or 1
+    per_step = max(workers, 16)                       # bounded sample: >= 16 images per spec per step
+    imgs = host_sample(per_step, 1002)
+    times = []
+    for i in range(args.warmup + args.steps):
+        v, dt = cpu_reference(imgs, SPECS, workers)
+        if i >= args.warmup:
+            times.append(dt)
+    mpix_step = per_step * len(SPECS) * H * W / 1e6
+    t = float(np.mean(times))
+    value = mpix_step / t
+    sample = "%d images of %dx%d per spec per step (of %d), %d processes, cv2 threads=1 each" % (
+        per_step, H, W, N_IMAGES, workers)
+    line = {"impl": "reference", "metric": "Mpixels/s per noise x denoise (mean over the step's combos)",
+            "value": value, "unit": "Mpix/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64 noise + u8 filters (NumPy/OpenCV)", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "specs": SPECS, "sample": sample},
+            "cpu_baseline": {"value": value, "unit": "Mpix/s", "cores": workers, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+    return 0
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from image_denoising_b200 import _lib, api
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (there is no CPU fallback for --impl b200)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L = _lib.lib()
+
+    batch = smooth_batch_torch(N_IMAGES, H, W, dev, 1002 + rank)
+    out = torch.empty_like(batch)
+    first = rank * N_IMAGES
+    plans = [api.Plan(N_IMAGES, H, W, s, local) for s in SPECS]
+    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
+        os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+    peak_gbs, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        for p in plans:
+            p.run(batch, out, SEED, first)
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(SPECS) + 1)] for _ in range(args.steps)]
+    clocks = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        clocks.start()
+    L.b2d_reset_launch_count()
+    t0 = torch.cuda.Event(enable_timing=True)
+    t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for k in range(args.steps):
+        ev[k][0].record()
+        for j, p in enumerate(plans):
+            p.run(batch, out, SEED, first)
+            ev[k][j + 1].record()
+    t1.record()
+    barrier()
+    launches = int(L.b2d_launch_count())
+    clk = clocks.stop() if rank == 0 else None
+    ms_total = t0.elapsed_time(t1)
+    tt = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms_step = tt.item() / args.steps
+    per_kernel = [float(np.mean([ev[k][j].elapsed_time(ev[k][j + 1]) for k in range(args.steps)]))
+                  for j in range(len(SPECS))]
+    mpix_batch = N_IMAGES * H * W / 1e6
+    value = world * len(SPECS) * mpix_batch / (ms_step * 1e-3)
+
+    # ---- end to end through the host-buffer C ABI call (b2d_run_host), pinned memory ----
+    h_in = torch.empty((N_IMAGES, H, W, 3), dtype=torch.uint8).pin_memory()
+    h_out = torch.empty_like(h_in).pin_memory()
+    h_in.copy_(batch.cpu())
+    e2e_steps = 0 if args.profile else max(1, min(args.steps, 3))
+    if args.profile:
+        print(json.dumps({"profile_run": True, "ms_per_step": ms_step, "per_spec_ms": dict(zip(SPECS, per_kernel)),
+                          "gpu_launches": launches}))
+        return 0
+    for p in plans:
+        p.run_host(h_in, h_out, SEED, first)                       # warm-up (allocates staging buffers)
+    barrier()
+    w0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        for p in plans:
+            p.run_host(h_in, h_out, SEED, first)
+    torch.cuda.synchronize()
+    e2e_s = (time.perf_counter() - w0) / e2e_steps
+    te = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = world * len(SPECS) * mpix_batch / te.item()
+    nbytes = batch.numel()
+
+    # ---- per-image checksums gathered over NCCL (the only cross-GPU payload, 8 B/image) ----
+    cs, _ = plans[-1].stats(out)
+    if world > 1:
+        allcs = [torch.empty_like(cs) for _ in range(world)]
+        dist.all_gather(allcs, cs)
+        cs = torch.cat(allcs)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    dom = int(np.argmax(per_kernel))
+    achieved = mpix_batch * 1e6 * ALGO_BYTES_PER_PIXEL / (per_kernel[dom] * 1e-3) / 1e9
+    cpu = None
+    if world == 1:
+        workers = os.cpu_count() or 1
+        n_s = max(workers, 16)
+        v, dt = cpu_reference(host_sample(n_s, 1002), SPECS, workers)
+        cpu = {"value": v, "unit": "Mpix/s", "cores": workers, "kind": "port",
+               "sample": "%d of %d images per spec, %d processes, cv2 threads=1 each, %.1f s" % (n_s, N_IMAGES, workers, dt)}
+    line = {"metric": "Mpixels/s per noise x denoise (mean over the step's combos)", "value": value, "unit": "Mpix/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8 (fp32 noise math)",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "specs": SPECS, "seed": SEED,
+                       "l2": "inputs 921.6 MB per GPU > 126 MB L2, no flush needed",
+                       "per_spec_ms": dict(zip(SPECS, per_kernel)),
+                       "per_spec_mpix_s": {s: mpix_batch / (t * 1e-3) for s, t in zip(SPECS, per_kernel)},
+                       "checksum_xor": int(np.bitwise_xor.reduce(cs.cpu().numpy()))},
+            "clocks": clk, "gpu_launches": launches,
+            "e2e": {"value": e2e_value, "unit": "Mpix/s", "h2d_bytes_per_step": len(SPECS) * nbytes,
+                    "d2h_bytes_per_step": len(SPECS) * nbytes, "api": "b2d_run_host (pinned host buffers)"},
+            "roofline": {"bound": "hbm", "kernel": "k_fused3<%s>" % SPECS[dom], "achieved": achieved,
+                         "peak": peak_gbs, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak_gbs,
+                         "traffic": None},
+            "cpu_baseline": cpu}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--profile", action="store_true", help="device-timed part only (for runs under ncu)")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    return run_reference(args) if args.impl == "reference" else run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
