@@ -1,0 +1,147 @@
+// b2d_median.cu - cv2.medianBlur(u8, k) for k = 5, 7 (BASELINE config 5 uses
+// k = 7; the reference itself only calls k = 3, lib/roi_data_layer/minibatch.py:153,
+// which is fused in b2d_fused3.cu).  Per channel median of the k x k window,
+// border REPLICATE (OpenCV's medianBlur border for every k).
+//
+// Method: register "forgetful selection" (Perrot, Domas, Couturier 2014): keep
+// ceil(n/2)+1 candidates, repeatedly drop their min and max (neither can be the
+// median) and insert the next window element; the last three give the median.
+// The network is data independent, so it runs on 2 x u16 lanes per register
+// (even / odd bytes of a 4-byte output word; VIMNMX.U16x2 is native on sm_100a,
+// u8x4 min/max is not).  INT-pipe bound: report against the FP32/INT roofline.
+#include "b2d_denoise.cuh"
+#include "b2d_plan.h"
+
+namespace b2d {
+
+constexpr int MD_THREADS = 256;
+constexpr int MD_TILE_WB = MD_THREADS * 4;
+constexpr int MD_TILE_H = 16;
+constexpr int MD_APRON = 16;                       // >= 3 * 3 bytes, multiple of 4
+constexpr int MD_SROW = MD_TILE_WB + 2 * MD_APRON;
+
+__device__ __forceinline__ void ce(uint32_t& a, uint32_t& b) {
+  const uint32_t lo = __vminu2(a, b);
+  b = __vmaxu2(a, b);
+  a = lo;
+}
+
+// min of a[0..M) -> a[0], max -> a[M-1]; all elements preserved
+template <int M, int CAP>
+__device__ __forceinline__ void minmax(uint32_t (&a)[CAP]) {
+  constexpr int half = (M + 1) / 2;
+#pragma unroll
+  for (int i = 0; i < M / 2; ++i) ce(a[i], a[i + half]);
+  if (M & 1) ce(a[half - 1], a[M - 1]);
+#pragma unroll
+  for (int i = 1; i < half; ++i) ce(a[0], a[i]);
+#pragma unroll
+  for (int i = half; i < M - 1; ++i) ce(a[i], a[M - 1]);
+}
+
+template <int M, int CAP, int N>
+struct Forget {
+  // a[0..M) are candidates, `next` indexes the next unseen window element
+  template <class Get>
+  static __device__ __forceinline__ uint32_t run(uint32_t (&a)[CAP], Get get) {
+    if constexpr (M == 3) {
+      return __vmaxu2(__vminu2(a[0], a[1]), __vminu2(__vmaxu2(a[0], a[1]), a[2]));
+    } else {
+      minmax<M, CAP>(a);
+      a[0] = get(N - (M - 3));          // elements CAP .. N-1 are inserted in order as M shrinks from CAP to 4
+      return Forget<M - 1, CAP, N>::run(a, get);
+    }
+  }
+};
+
+template <int K>
+__global__ void __launch_bounds__(MD_THREADS) k_median(ImageSet s) {
+  constexpr int R = K / 2, N = K * K, CAP = (N + 1) / 2 + 1;
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int tid = threadIdx.x;
+  const int c0 = blockIdx.x * MD_TILE_WB, y0 = blockIdx.y * MD_TILE_H;
+  const int img_local = image_of(s, blockIdx.z);
+  const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
+  const int rows = MD_TILE_H + 2 * R;
+
+  // tile + apron, REPLICATE border resolved per byte (pixel clamp keeps the channel)
+  for (int it = tid; it < rows * (MD_SROW / 4); it += MD_THREADS) {
+    const int tr = it / (MD_SROW / 4), wc = it - tr * (MD_SROW / 4);
+    const int y = min(max(y0 - R + tr, 0), s.h - 1);
+    const uint8_t* row = img + (uint64_t)y * s.rowbytes;
+    const int c = c0 - MD_APRON + 4 * wc;
+    uint32_t w;
+    if (c >= 0 && c + 4 <= s.rowbytes && ((reinterpret_cast<uintptr_t>(row + c) & 3u) == 0)) {
+      w = __ldg(reinterpret_cast<const uint32_t*>(row + c));
+    } else {
+      uint32_t b[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int cc = c + k;
+        int px = cc >= 0 ? cc / 3 : -((-cc + 2) / 3);
+        const int ch = cc - 3 * px;
+        px = min(max(px, 0), s.w - 1);
+        b[k] = __ldg(row + px * 3 + ch);
+      }
+      w = pack4(b[0], b[1], b[2], b[3]);
+    }
+    *reinterpret_cast<uint32_t*>(smem + tr * MD_SROW + 4 * wc) = w;
+  }
+  __syncthreads();
+
+  const int c = c0 + 4 * tid;
+  if (c >= s.rowbytes) return;
+  const uint8_t* sp = smem + MD_APRON + 4 * tid;
+  const int nrows = min(MD_TILE_H, s.h - y0);
+  for (int r = 0; r < nrows; ++r) {
+    // window element e = (dy, dx): bytes at row r + dy, byte offset 3 * (dx - R)
+    uint32_t win[N];
+#pragma unroll
+    for (int dy = 0; dy < K; ++dy) {
+      const uint8_t* rp = sp + (r + dy) * MD_SROW;
+      uint32_t al[2 * R + 2];                       // aligned words covering bytes [-4R, 4R + 4)
+#pragma unroll
+      for (int q = 0; q < 2 * R + 2; ++q) al[q] = *reinterpret_cast<const uint32_t*>(rp + 4 * (q - R));
+#pragma unroll
+      for (int dx = 0; dx < K; ++dx) {
+        const int off = 3 * (dx - R) + 4 * R;       // byte offset from al[0], >= 0
+        const int q = off / 4, sh = off % 4;
+        win[dy * K + dx] = sh == 0 ? al[q] : __byte_perm(al[q], al[q + 1], sh == 1 ? 0x4321 : sh == 2 ? 0x5432 : 0x6543);
+      }
+    }
+    uint32_t res[2];
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      auto get = [&](int e) { return half ? __byte_perm(win[e], 0u, 0x4341) : __byte_perm(win[e], 0u, 0x4240); };
+      uint32_t a[CAP];
+#pragma unroll
+      for (int e = 0; e < CAP; ++e) a[e] = get(e);
+      res[half] = Forget<CAP, CAP, N>::run(a, get);
+    }
+    const uint32_t o = __byte_perm(res[0], res[1], 0x6240);
+    uint8_t* op = s.out + (uint64_t)img_local * s.elems + (uint64_t)(y0 + r) * s.rowbytes + c;
+    if (c + 4 <= s.rowbytes && (reinterpret_cast<uintptr_t>(op) & 3u) == 0) {
+      *reinterpret_cast<uint32_t*>(op) = o;
+    } else {
+      for (int k = 0; k < 4 && c + k < s.rowbytes; ++k) op[k] = (uint8_t)(o >> (8 * k));
+    }
+  }
+}
+
+template <int K>
+static cudaError_t launch_median_t(const ImageSet& s, cudaStream_t st) {
+  const dim3 grid((s.rowbytes + MD_TILE_WB - 1) / MD_TILE_WB, (s.h + MD_TILE_H - 1) / MD_TILE_H, s.count);
+  const size_t smem = (size_t)(MD_TILE_H + 2 * (K / 2)) * MD_SROW;
+  k_median<K><<<grid, MD_THREADS, smem, st>>>(s);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_median_k(const ImageSet& s, int k, cudaStream_t st) {
+  if (s.count <= 0) return cudaSuccess;
+  if (k == 5) return launch_median_t<5>(s, st);
+  if (k == 7) return launch_median_t<7>(s, st);
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace b2d

@@ -106,6 +106,7 @@ extern "C" int b2d_plan_create(b2d_plan** out, int device, int n, int h, int w, 
   p->off_scan = off;   off = align_up(off + (p->need_aux ? sizeof(double) * (size_t)p->brown_chunks * n : 0), 256);
   p->off_stage = off;  off = align_up(off + (size_t)p->elems * n, 256);
   p->off_aux = off;    off = align_up(off + (p->need_aux ? (size_t)p->elems * n : 0), 256);
+  p->off_denoise = off;
   off += denoise_workspace_bytes(*p);
   p->ws_bytes = off;
   *out = p;
