@@ -199,7 +199,9 @@ extern "C" int b2d_run_host(b2d_plan* plan, const uint8_t* h_in, uint8_t* h_out,
   }
   // chunks of >= 32 MiB (at least one image) so each copy runs at full PCIe rate
   int per = (int)std::max<uint64_t>(1, (32ull << 20) / plan->elems);
-  if (plan->need_aux) per = plan->n;  // pre-pass workspaces are batch-indexed but shared: keep one chunk
+  bool shared_ws = plan->need_aux;    // pre-pass / wavelet workspaces are shared by the whole batch: keep one chunk
+  for (const SpecGroup& g : plan->groups) shared_ws = shared_ws || g.spec.denoise == B2D_DENOISE_WAVELET;
+  if (shared_ws) per = plan->n;
   int k = 0;
   for (int img0 = 0; img0 < plan->n; img0 += per, ++k) {
     const int cnt = std::min(per, plan->n - img0);

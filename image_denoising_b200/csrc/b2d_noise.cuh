@@ -55,7 +55,7 @@ struct NoiseOp;
 // ---- identity (retain_original, minibatch.py:1512-1516) -------------------
 template <int MODE>
 struct NoiseOp<NK_NONE, MODE> {
-  static __device__ __forceinline__ void apply8(const NoiseArgs&, const GroupCtx&, uint32_t (&)[8]) {}
+  static __device__ __forceinline__ void apply8(const NoiseArgs&, const GroupCtx&, uint32_t (&)[8], float* = nullptr) {}
 };
 
 // element index helpers for field access
@@ -70,7 +70,8 @@ __device__ __forceinline__ bool in_image(const NoiseArgs& a, const GroupCtx& g, 
 // ---- speckle:  clip(f + f * N(0, sqrt(var)), 0, 1)   (minibatch.py:380-383)
 template <int MODE, bool SPECKLE>
 struct NormalNoise {
-  static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8]) {
+  static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8],
+                                                float* xf = nullptr) {
     if (MODE == NM_INJECT) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
@@ -79,6 +80,7 @@ struct NormalNoise {
         const double f = (double)v[i] / 255.0;
         double o = SPECKLE ? __dadd_rn(f, __dmul_rn(f, n)) : __dadd_rn(f, n);
         o = fmin(fmax(o, 0.0), 1.0);
+        if (xf) xf[i] = (float)__dmul_rn(255.0, o);
         v[i] = wrap_u8(__dmul_rn(255.0, o));
       }
       return;
@@ -96,8 +98,10 @@ struct NormalNoise {
       const float v0 = (float)v[2 * j], v1 = (float)v[2 * j + 1];
       const float x0 = SPECKLE ? fmaf(v0, n0, v0) : fmaf(n0, 255.0f, v0);
       const float x1 = SPECKLE ? fmaf(v1, n1, v1) : fmaf(n1, 255.0f, v1);
-      v[2 * j] = (uint32_t)__float2int_rz(fminf(fmaxf(x0, 0.0f), 255.0f));
-      v[2 * j + 1] = (uint32_t)__float2int_rz(fminf(fmaxf(x1, 0.0f), 255.0f));
+      const float c0 = fminf(fmaxf(x0, 0.0f), 255.0f), c1 = fminf(fmaxf(x1, 0.0f), 255.0f);
+      if (xf) { xf[2 * j] = c0; xf[2 * j + 1] = c1; }
+      v[2 * j] = (uint32_t)__float2int_rz(c0);
+      v[2 * j + 1] = (uint32_t)__float2int_rz(c1);
     }
   }
 };
@@ -108,7 +112,8 @@ template <int MODE> struct NoiseOp<NK_SPECKLE, MODE> : NormalNoise<MODE, true> {
 // generator: 15 bits decide the flip, 1 bit salt/pepper.
 template <int MODE>
 struct NoiseOp<NK_SAP, MODE> {
-  static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8]) {
+  static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8],
+                                                float* xf = nullptr) {
     if (MODE == NM_INJECT) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
@@ -137,18 +142,21 @@ struct NoiseOp<NK_SAP, MODE> {
 //   uniform  cv2.add(f, U(0, high))                 (minibatch.py:676-677,710)
 //   rayleigh cv2.add(f, rayleigh.rvs(scale))        (minibatch.py:1356-1357,1387)
 //   gamma    cv2.add(f, gamma.rvs(1.99, scale))     (minibatch.py:1216-1217,1247)
-__device__ __forceinline__ uint32_t add_wrap_inject(uint32_t v, double s) {
+__device__ __forceinline__ uint32_t add_wrap_inject(uint32_t v, double s, float* xf) {
   const double f = (double)v / 255.0;
-  return wrap_u8(__dmul_rn(255.0, __dadd_rn(f, s)));
+  const double x = __dmul_rn(255.0, __dadd_rn(f, s));
+  if (xf) *xf = (float)x;
+  return wrap_u8(x);
 }
 
 template <int MODE>
 struct NoiseOp<NK_UNIFORM, MODE> {
-  static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8]) {
+  static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8],
+                                                float* xf = nullptr) {
     if (MODE == NM_INJECT) {
 #pragma unroll
       for (int i = 0; i < 8; ++i)
-        if (in_image(a, g, i)) v[i] = add_wrap_inject(v[i], a.f0[field_index(a, g, i)]);
+        if (in_image(a, g, i)) v[i] = add_wrap_inject(v[i], a.f0[field_index(a, g, i)], xf ? xf + i : nullptr);
       return;
     }
     const uint4 r = group_random(a, g, 0);
@@ -156,18 +164,21 @@ struct NoiseOp<NK_UNIFORM, MODE> {
     for (int i = 0; i < 8; ++i) {
       const float s = a.p0 * u16_to_unit(r16(r, i));
       if (MODE == NM_DUMP && in_image(a, g, i)) a.dump0[field_index(a, g, i)] = s;
-      v[i] = wrap_u8(fmaf(s, 255.0f, (float)v[i]));
+      const float x = fmaf(s, 255.0f, (float)v[i]);
+      if (xf) xf[i] = x;
+      v[i] = wrap_u8(x);
     }
   }
 };
 
 template <int MODE>
 struct NoiseOp<NK_RAYLEIGH, MODE> {
-  static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8]) {
+  static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8],
+                                                float* xf = nullptr) {
     if (MODE == NM_INJECT) {
 #pragma unroll
       for (int i = 0; i < 8; ++i)
-        if (in_image(a, g, i)) v[i] = add_wrap_inject(v[i], a.f0[field_index(a, g, i)]);
+        if (in_image(a, g, i)) v[i] = add_wrap_inject(v[i], a.f0[field_index(a, g, i)], xf ? xf + i : nullptr);
       return;
     }
     const uint4 r = group_random(a, g, 0);
@@ -176,7 +187,9 @@ struct NoiseOp<NK_RAYLEIGH, MODE> {
       // inverse CDF: scale * sqrt(-2 ln u)
       const float s = a.p0 * fast_sqrt(-1.3862943611198906f * fast_lg2(u16_to_unit(r16(r, i))));
       if (MODE == NM_DUMP && in_image(a, g, i)) a.dump0[field_index(a, g, i)] = s;
-      v[i] = wrap_u8(fmaf(s, 255.0f, (float)v[i]));
+      const float x = fmaf(s, 255.0f, (float)v[i]);
+      if (xf) xf[i] = x;
+      v[i] = wrap_u8(x);
     }
   }
 };
@@ -186,11 +199,12 @@ struct NoiseOp<NK_RAYLEIGH, MODE> {
 // words 0,1 -> 4 normals, words 2,3 -> 4 acceptance uniforms.
 template <int MODE>
 struct NoiseOp<NK_GAMMA, MODE> {
-  static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8]) {
+  static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8],
+                                                float* xf = nullptr) {
     if (MODE == NM_INJECT) {
 #pragma unroll
       for (int i = 0; i < 8; ++i)
-        if (in_image(a, g, i)) v[i] = add_wrap_inject(v[i], a.f0[field_index(a, g, i)]);
+        if (in_image(a, g, i)) v[i] = add_wrap_inject(v[i], a.f0[field_index(a, g, i)], xf ? xf + i : nullptr);
       return;
     }
     const float d = 1.99f - 1.0f / 3.0f;
@@ -229,7 +243,9 @@ struct NoiseOp<NK_GAMMA, MODE> {
     for (int i = 0; i < 8; ++i) {
       const float s = a.p0 * smp[i];
       if (MODE == NM_DUMP && in_image(a, g, i)) a.dump0[field_index(a, g, i)] = s;
-      v[i] = wrap_u8(fmaf(s, 255.0f, (float)v[i]));
+      const float x = fmaf(s, 255.0f, (float)v[i]);
+      if (xf) xf[i] = x;
+      v[i] = wrap_u8(x);
     }
   }
 };
@@ -274,7 +290,8 @@ __device__ __forceinline__ float poisson_ptrs_try(float lam, float U01, float V)
 
 template <int MODE>
 struct NoiseOp<NK_POISSON, MODE> {
-  static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8]) {
+  static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8],
+                                                float* xf = nullptr) {
     const float vals = a.img_par[g.img_local];
     if (MODE == NM_INJECT) {
 #pragma unroll
@@ -324,7 +341,8 @@ struct NoiseOp<NK_POISSON, MODE> {
 // image (periodic: depends on H, W, L only) or one per image (brownian).
 template <int MODE>
 struct NoiseOp<NK_TABLE_ADD, MODE> {
-  static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8]) {
+  static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8],
+                                                float* xf = nullptr) {
     const uint8_t* t = a.tab + (uint64_t)g.img_local * a.tab_stride + (uint64_t)g.group * 8u;
     if ((uint64_t)g.group * 8u + 8u <= a.elems && ((reinterpret_cast<uintptr_t>(t) & 7u) == 0)) {
       const uint2 w = *reinterpret_cast<const uint2*>(t);
@@ -343,7 +361,8 @@ struct NoiseOp<NK_TABLE_ADD, MODE> {
 // pixel is min(255, 3 * BGR[2 - c]) unless u0 = 1 (keep BGR).
 template <int MODE>
 struct NoiseOp<NK_SHADER, MODE> {
-  static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8]) {
+  static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8],
+                                                float* xf = nullptr) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const uint64_t e = (uint64_t)g.group * 8u + i;
@@ -356,5 +375,26 @@ struct NoiseOp<NK_SHADER, MODE> {
     }
   }
 };
+
+
+// float view of the noised values (0..255 scale, BEFORE the ->u8 cast) for the
+// consumers that the reference feeds with the float image (denoise_wavelet on
+// random_noise / cv2.add output, minibatch.py:91-94,677-679).  Operators whose
+// reference result is already uint8 (s&p values, poisson_wavelet's explicit
+// ->u8 at minibatch.py:212, periodic, brownian, shader) return the uint8 value.
+template <int KIND, int MODE>
+__device__ __forceinline__ void apply8_float(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8], float (&xf)[8]) {
+  constexpr bool kFloat = KIND == NK_GAUSSIAN || KIND == NK_SPECKLE || KIND == NK_UNIFORM || KIND == NK_RAYLEIGH ||
+                          KIND == NK_GAMMA;
+  if (kFloat) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) xf[i] = (float)v[i];
+    NoiseOp<KIND, MODE>::apply8(a, g, v, xf);
+  } else {
+    NoiseOp<KIND, MODE>::apply8(a, g, v);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) xf[i] = (float)v[i];
+  }
+}
 
 }  // namespace b2d

@@ -1,0 +1,512 @@
+// b2d_wavelet.cu - skimage.restoration.denoise_wavelet(x, method='BayesShrink',
+// mode='soft', wavelet in {'bior1.5' (live files), 'db1' (backups, BASELINE C4)},
+// [wavelet_levels=3,] multichannel=True, convert2ycbcr=True) followed by the
+// reference's (255 * out).astype(np.uint8)   (lib/roi_data_layer/minibatch.py:92-96,
+// lib/model/test.py_bkp:1913-1916).  Algorithm restated in oracle/wavelet.py.
+//
+// General path (any wavelet / level count / odd sizes), fp32 planes in the
+// caller's workspace, float64 only for the energy sums:
+//   1. noise (float, unquantised where the reference keeps floats) -> "YCbCr" of the
+//      array's own channel order (quirk Q7) -> 3 planes + per-channel min / max
+//   2. L levels of separable DWT, pywt mode 'symmetric'
+//   3. sigma = median(|dd_1| != 0) / 0.6745 by 3-pass radix select; per band energy
+//   4. inverse DWT with soft thresholding applied while reading the detail bands
+//   5. clip to the channel's [min, max], YCbCr -> RGB, clip [0, 1], * 255, truncate
+// The per-channel normalisation to [0, 1] is affine and the DWT is linear, so
+// it is folded into the thresholds (thr_un = var / sqrt(max(dvar - var, eps * s^2)),
+// s = max - min) and the clip range instead of being a pass of its own.
+#include "b2d_denoise.cuh"
+#include "b2d_plan.h"
+#include "b2d_wavelet.cuh"
+
+#include <algorithm>
+#include <cmath>
+
+namespace b2d {
+
+// ---------------------------------------------------------------- geometry --
+static const double kS = 0.7071067811865476, kC1 = 0.01657281518405971, kC2 = 0.12153397801643787;
+
+void wavelet_geometry(WvGeom& g, int wavelet, int levels_req, int h, int w) {
+  g.F = wavelet == B2D_WAVELET_DB1 ? 2 : 10;
+  const double db1[4][2] = {{kS, kS}, {-kS, kS}, {kS, kS}, {kS, -kS}};
+  const double bior[4][10] = {
+      {kC1, -kC1, -kC2, kC2, kS, kS, kC2, -kC2, -kC1, kC1},
+      {0, 0, 0, 0, -kS, kS, 0, 0, 0, 0},
+      {0, 0, 0, 0, kS, kS, 0, 0, 0, 0},
+      {kC1, kC1, -kC2, -kC2, kS, -kS, kC2, kC2, -kC1, -kC1}};
+  for (int k = 0; k < 4; ++k)
+    for (int j = 0; j < WV_MAXF; ++j) {
+      const double v = j < g.F ? (g.F == 2 ? db1[k][j] : bior[k][j]) : 0.0;
+      (k == 0 ? g.dec_lo : k == 1 ? g.dec_hi : k == 2 ? g.rec_lo : g.rec_hi)[j] = (float)v;
+    }
+  int L = levels_req;
+  if (L <= 0) {   // skimage: max(min(dwt_max_level(s, F)) - 3, 1)
+    auto maxlev = [&](int n) { return n < g.F - 1 ? 0 : (int)std::floor(std::log2((double)n / (g.F - 1.0))); };
+    L = std::max(std::min(maxlev(h), maxlev(w)) - 3, 1);
+  }
+  g.L = std::min(L, WV_MAXL);
+  g.h[0] = h; g.w[0] = w;
+  for (int l = 1; l <= g.L; ++l) {
+    g.h[l] = (g.h[l - 1] + g.F - 1) / 2;
+    g.w[l] = (g.w[l - 1] + g.F - 1) / 2;
+  }
+  // per-channel float offsets
+  const size_t HW = (size_t)h * w;
+  const size_t T = g.L >= 1 ? std::max((size_t)h * g.w[1], (size_t)g.h[1] * w) : HW;   // row-pass temporaries, both directions
+  size_t off = 0;
+  g.off_plane = off; off += HW;
+  g.off_tlo = off;   off += T;
+  g.off_thi = off;   off += T;
+  for (int l = 1; l <= g.L; ++l) {
+    const size_t S = (size_t)g.h[l] * g.w[l];
+    g.off_app[l] = off; off += S;
+    for (int b = 0; b < 3; ++b) { g.off_det[l][b] = off; off += S; }
+  }
+  g.chan_floats = (off + 3) & ~(size_t)3;
+}
+
+// ordered-int encoding so atomicMin/atomicMax work on floats of either sign
+__device__ __forceinline__ int f2ord(float f) {
+  const int b = __float_as_int(f);
+  return b ^ ((b >> 31) & 0x7fffffff);
+}
+__device__ __forceinline__ float ord2f(int o) { return __int_as_float(o ^ ((o >> 31) & 0x7fffffff)); }
+
+// skimage.color.rgb2ycbcr matrix (BT.601 studio swing), applied to channels in array order
+__constant__ float kYCC[3][3] = {{65.481f, 128.553f, 24.966f}, {-37.797f, -74.203f, 112.0f}, {112.0f, -93.786f, -18.214f}};
+
+// ------------------------------------------------- 1. noise + colour + min/max
+template <int KIND, int MODE>
+__global__ void __launch_bounds__(256) k_wv_color(ImageSet s, NoiseArgs na, WvGeom g, float* ws, WvStats* stats,
+                                                  int chunk_first) {
+  const int z = blockIdx.z;                                   // image inside the chunk
+  const int img_local = image_of(s, chunk_first + z);
+  const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
+  float* base = ws + (size_t)z * 3 * g.chan_floats;
+  float mn[3] = {3.0e38f, 3.0e38f, 3.0e38f}, mx[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+  // 24 bytes = 8 pixels = 3 noise groups per thread iteration
+  const uint64_t npix = (uint64_t)s.h * s.w;
+  for (uint64_t p8 = (uint64_t)blockIdx.x * 256 + threadIdx.x; p8 * 8 < npix; p8 += (uint64_t)gridDim.x * 256) {
+    float xf[24];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+      const uint32_t grp = (uint32_t)(p8 * 3 + q);
+      uint32_t v[8];
+      float f[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const uint64_t e = (uint64_t)grp * 8 + i;
+        v[i] = e < s.elems ? (uint32_t)__ldg(img + e) : 0u;
+      }
+      GroupCtx gc{(uint32_t)img_local, grp, img};
+      apply8_float<KIND, MODE>(na, gc, v, f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) xf[8 * q + i] = f[i] * (1.0f / 255.0f);
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint64_t pix = p8 * 8 + k;
+      if (pix >= npix) break;
+      const float c0 = xf[3 * k], c1 = xf[3 * k + 1], c2 = xf[3 * k + 2];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float y = kYCC[c][0] * c0 + kYCC[c][1] * c1 + kYCC[c][2] * c2 + (c == 0 ? 16.0f : 128.0f);
+        base[(size_t)c * g.chan_floats + g.off_plane + pix] = y;
+        mn[c] = fminf(mn[c], y);
+        mx[c] = fmaxf(mx[c], y);
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    for (int o = 16; o; o >>= 1) {
+      mn[c] = fminf(mn[c], __shfl_xor_sync(0xffffffffu, mn[c], o));
+      mx[c] = fmaxf(mx[c], __shfl_xor_sync(0xffffffffu, mx[c], o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+      atomicMin(&stats[z * 3 + c].mn_ord, f2ord(mn[c]));
+      atomicMax(&stats[z * 3 + c].mx_ord, f2ord(mx[c]));
+    }
+  }
+}
+
+// ------------------------------------------------------------ 2. forward DWT
+// Products and sums are rounded separately (no FMA): pywt / NumPy do the same, and it
+// keeps coefficients that cancel exactly (duplicated border samples, flat regions)
+// exactly zero - _sigma_est_dwt drops exact zeros before taking the median.
+// pywt 'symmetric' (half-sample) extension
+__device__ __forceinline__ int sym_ext(int i, int n) {
+  const int p = 2 * n;
+  int m = i % p;
+  if (m < 0) m += p;
+  return m < n ? m : p - 1 - m;
+}
+
+// along x: in [h x w] -> lo, hi [h x wo];  out[i] = sum_j filt[j] * x[ext(2 i + 1 - j)]
+__global__ void __launch_bounds__(256) k_dwt_rows(WvGeom g, float* ws, int level, size_t in_off) {
+  const int h = g.h[level - 1], w = g.w[level - 1], wo = g.w[level];
+  float* base = ws + (size_t)blockIdx.z * g.chan_floats;
+  const float* in = base + in_off;
+  float* lo = base + g.off_tlo;
+  float* hi = base + g.off_thi;
+  const int total = h * wo;
+  for (int t = blockIdx.x * 256 + threadIdx.x; t < total; t += gridDim.x * 256) {
+    const int y = t / wo, i = t - y * wo;
+    const float* row = in + (size_t)y * w;
+    float a = 0.f, d = 0.f;
+    if (2 * i + 1 - (g.F - 1) >= 0 && 2 * i + 1 < w) {
+#pragma unroll
+      for (int j = 0; j < WV_MAXF; ++j)
+        if (j < g.F) { const float x = row[2 * i + 1 - j]; a = __fadd_rn(a, __fmul_rn(g.dec_lo[j], x)); d = __fadd_rn(d, __fmul_rn(g.dec_hi[j], x)); }
+    } else {
+      for (int j = 0; j < g.F; ++j) {
+        const float x = row[sym_ext(2 * i + 1 - j, w)];
+        a = __fadd_rn(a, __fmul_rn(g.dec_lo[j], x));
+        d = __fadd_rn(d, __fmul_rn(g.dec_hi[j], x));
+      }
+    }
+    lo[t] = a;
+    hi[t] = d;
+  }
+}
+
+// along y: lo, hi [h x wo] -> aa (app), da, ad, dd [ho x wo]
+__global__ void __launch_bounds__(256) k_dwt_cols(WvGeom g, float* ws, int level) {
+  const int h = g.h[level - 1], wo = g.w[level], ho = g.h[level];
+  float* base = ws + (size_t)blockIdx.z * g.chan_floats;
+  const float* lo = base + g.off_tlo;
+  const float* hi = base + g.off_thi;
+  float* aa = base + g.off_app[level];
+  float* da = base + g.off_det[level][0];     // detail along axis 0 (y), approx along x
+  float* ad = base + g.off_det[level][1];     // approx along y, detail along x
+  float* dd = base + g.off_det[level][2];
+  const int total = ho * wo;
+  for (int t = blockIdx.x * 256 + threadIdx.x; t < total; t += gridDim.x * 256) {
+    const int i = t / wo, x = t - i * wo;
+    float s_aa = 0.f, s_da = 0.f, s_ad = 0.f, s_dd = 0.f;
+    for (int j = 0; j < g.F; ++j) {
+      const int y = sym_ext(2 * i + 1 - j, h);
+      const float l = lo[(size_t)y * wo + x], hv = hi[(size_t)y * wo + x];
+      s_aa = __fadd_rn(s_aa, __fmul_rn(g.dec_lo[j], l));
+      s_da = __fadd_rn(s_da, __fmul_rn(g.dec_hi[j], l));
+      s_ad = __fadd_rn(s_ad, __fmul_rn(g.dec_lo[j], hv));
+      s_dd = __fadd_rn(s_dd, __fmul_rn(g.dec_hi[j], hv));
+    }
+    aa[t] = s_aa; da[t] = s_da; ad[t] = s_ad; dd[t] = s_dd;
+  }
+}
+
+// ------------------------------------------------------- 3. band statistics
+__global__ void __launch_bounds__(256) k_band_energy(WvGeom g, const float* ws, WvStats* stats, int level) {
+  const float* base = ws + (size_t)blockIdx.z * g.chan_floats;
+  const int n = g.h[level] * g.w[level];
+  double e[3] = {0, 0, 0};
+  for (int t = blockIdx.x * 256 + threadIdx.x; t < n; t += gridDim.x * 256)
+#pragma unroll
+    for (int b = 0; b < 3; ++b) {
+      const float d = base[g.off_det[level][b] + t];
+      e[b] += (double)d * d;
+    }
+#pragma unroll
+  for (int b = 0; b < 3; ++b) {
+    for (int o = 16; o; o >>= 1) e[b] += __shfl_xor_sync(0xffffffffu, e[b], o);
+    if ((threadIdx.x & 31) == 0) atomicAdd(&stats[blockIdx.z].energy[level][b], e[b]);
+  }
+}
+
+// radix select over the bit patterns of |dd_1| (non-zero only): pass 0 bits 30..20,
+// pass 1 bits 19..9, pass 2 bits 8..0; two ranks are tracked for even counts
+__global__ void __launch_bounds__(256) k_select_hist(WvGeom g, const float* ws, const WvStats* stats,
+                                                     unsigned int* hist, int pass) {
+  __shared__ unsigned int sh[2][WV_BINS];
+  for (int i = threadIdx.x; i < 2 * WV_BINS; i += 256) (&sh[0][0])[i] = 0u;
+  __syncthreads();
+  const float* dd = ws + (size_t)blockIdx.z * g.chan_floats + g.off_det[1][2];
+  const int n = g.h[1] * g.w[1];
+  const int shift = pass == 0 ? 20 : pass == 1 ? 9 : 0;
+  const unsigned int mask = pass == 2 ? 0x1ffu : 0x7ffu;
+  const unsigned int p0 = stats[blockIdx.z].prefix[0], p1 = stats[blockIdx.z].prefix[1];
+  const int hshift = pass == 0 ? 31 : pass == 1 ? 20 : 9;     // bits above the current digit
+  for (int t = blockIdx.x * 256 + threadIdx.x; t < n; t += gridDim.x * 256) {
+    const unsigned int b = __float_as_uint(dd[t]) & 0x7fffffffu;
+    if (b == 0u) continue;
+    const unsigned int digit = (b >> shift) & mask;
+    const unsigned int high = pass == 0 ? 0u : (b >> hshift);
+    if (pass == 0 || high == p0) atomicAdd(&sh[0][digit], 1u);
+    if (pass != 0 && high == p1) atomicAdd(&sh[1][digit], 1u);
+  }
+  __syncthreads();
+  unsigned int* gh = hist + (size_t)blockIdx.z * 2 * WV_BINS;
+  for (int i = threadIdx.x; i < 2 * WV_BINS; i += 256)
+    if ((&sh[0][0])[i]) atomicAdd(&gh[i], (&sh[0][0])[i]);
+}
+
+__global__ void k_select_step(WvStats* stats, unsigned int* hist, int pass, int nplanes) {
+  const int z = blockIdx.x * blockDim.x + threadIdx.x;
+  if (z >= nplanes) return;
+  WvStats& st = stats[z];
+  unsigned int* h0 = hist + (size_t)z * 2 * WV_BINS;
+  const int bins = pass == 2 ? 512 : WV_BINS;
+  const int bits = pass == 2 ? 9 : 11;
+  if (pass == 0) {
+    unsigned long long n = 0;
+    for (int i = 0; i < bins; ++i) n += h0[i];
+    st.count = n;
+    st.rank[0] = n ? (n - 1) / 2 : 0;
+    st.rank[1] = n / 2;
+    st.prefix[0] = st.prefix[1] = 0u;
+  }
+  for (int r = 0; r < 2; ++r) {
+    const unsigned int* hh = (pass == 0) ? h0 : h0 + r * WV_BINS;
+    unsigned long long k = st.rank[r], acc = 0;
+    int sel = bins - 1;
+    for (int i = 0; i < bins; ++i) {
+      if (acc + hh[i] > k) { sel = i; break; }
+      acc += hh[i];
+    }
+    st.rank[r] = k - acc;
+    st.prefix[r] = (st.prefix[r] << bits) | (unsigned int)sel;
+  }
+  for (int i = 0; i < 2 * WV_BINS; ++i) h0[i] = 0u;            // ready for the next pass
+  if (pass == 2) {
+    const float v0 = __uint_as_float(st.prefix[0]), v1 = __uint_as_float(st.prefix[1]);
+    const double med = st.count ? 0.5 * ((double)v0 + (double)v1) : 0.0;
+    st.sigma = (float)(med / 0.6744897501960817);
+  }
+}
+
+// BayesShrink thresholds in un-normalised units (see header comment)
+__global__ void k_thresholds(WvGeom g, WvStats* stats, int nplanes) {
+  const int z = blockIdx.x * blockDim.x + threadIdx.x;
+  if (z >= nplanes) return;
+  WvStats& st = stats[z];
+  st.lo = ord2f(st.mn_ord);
+  st.hi = ord2f(st.mx_ord);
+  const double s = (double)st.hi - (double)st.lo;
+  const double var = (double)st.sigma * st.sigma;
+  const double eps = 2.220446049250313e-16 * s * s;
+  for (int l = 1; l <= g.L; ++l) {
+    const double n = (double)g.h[l] * g.w[l];
+    for (int b = 0; b < 3; ++b) {
+      const double dvar = st.energy[l][b] / n;
+      st.thr[l][b] = (float)(var / sqrt(fmax(dvar - var, eps)));
+    }
+  }
+}
+
+// ------------------------------------------------------------ 4. inverse DWT
+__device__ __forceinline__ float soft(float d, float thr) {
+  // pywt.threshold(d, thr, 'soft') = d * max(1 - thr / |d|, 0)
+  const float m = fabsf(d);
+  return m > 0.0f ? d * fmaxf(1.0f - thr / m, 0.0f) : 0.0f;
+}
+
+// one axis of pywt's idwt: out[k] = sum_i a[i] rec_lo[k + F - 2 - 2 i] + d[i] rec_hi[k + F - 2 - 2 i]
+template <class LoadA, class LoadD>
+__device__ __forceinline__ float idwt_tap(const WvGeom& g, int k, int m, LoadA la, LoadD ld) {
+  float acc = 0.f;
+  const int top = k + g.F - 2;
+  for (int j = top & 1; j < g.F; j += 2) {
+    const int i = (top - j) >> 1;
+    if (i < 0 || i >= m) continue;
+    acc = fmaf(g.rec_lo[j], la(i), acc);
+    acc = fmaf(g.rec_hi[j], ld(i), acc);
+  }
+  return acc;
+}
+
+// along x: (app, ad) -> tlo, (da, dd) -> thi, each [h_l x wr], wr = w_{l-1}; details soft-thresholded on read
+__global__ void __launch_bounds__(256) k_idwt_rows(WvGeom g, float* ws, const WvStats* stats, int level) {
+  const int hl = g.h[level], wl = g.w[level], wr = g.w[level - 1];
+  float* base = ws + (size_t)blockIdx.z * g.chan_floats;
+  const float* app = base + g.off_app[level];
+  const float* da = base + g.off_det[level][0];
+  const float* ad = base + g.off_det[level][1];
+  const float* dd = base + g.off_det[level][2];
+  const float t_da = stats[blockIdx.z].thr[level][0], t_ad = stats[blockIdx.z].thr[level][1],
+              t_dd = stats[blockIdx.z].thr[level][2];
+  float* lo = base + g.off_tlo;
+  float* hi = base + g.off_thi;
+  const int total = hl * wr;
+  for (int t = blockIdx.x * 256 + threadIdx.x; t < total; t += gridDim.x * 256) {
+    const int y = t / wr, k = t - y * wr;
+    const size_t r = (size_t)y * wl;
+    lo[t] = idwt_tap(g, k, wl, [&](int i) { return app[r + i]; }, [&](int i) { return soft(ad[r + i], t_ad); });
+    hi[t] = idwt_tap(g, k, wl, [&](int i) { return soft(da[r + i], t_da); }, [&](int i) { return soft(dd[r + i], t_dd); });
+  }
+}
+
+// along y: tlo, thi [h_l x wr] -> out [hr x wr], hr = h_{l-1}; out = app[l-1] or the plane
+__global__ void __launch_bounds__(256) k_idwt_cols(WvGeom g, float* ws, int level) {
+  const int hl = g.h[level], wr = g.w[level - 1], hr = g.h[level - 1];
+  float* base = ws + (size_t)blockIdx.z * g.chan_floats;
+  const float* lo = base + g.off_tlo;
+  const float* hi = base + g.off_thi;
+  float* out = base + (level == 1 ? g.off_plane : g.off_app[level - 1]);
+  const int total = hr * wr;
+  for (int t = blockIdx.x * 256 + threadIdx.x; t < total; t += gridDim.x * 256) {
+    const int k = t / wr, x = t - k * wr;
+    out[t] = idwt_tap(g, k, hl, [&](int i) { return lo[(size_t)i * wr + x]; },
+                      [&](int i) { return hi[(size_t)i * wr + x]; });
+  }
+}
+
+// ----------------------------------------------------------- 5. back to uint8
+struct WvFinalArgs { float inv[3][3]; };
+
+__global__ void __launch_bounds__(256) k_wv_final(ImageSet s, WvGeom g, const float* ws, const WvStats* stats,
+                                                  WvFinalArgs fa, int chunk_first) {
+  const int z = blockIdx.z;
+  const int img_local = image_of(s, chunk_first + z);
+  const float* base = ws + (size_t)z * 3 * g.chan_floats;
+  uint8_t* out = s.out + (uint64_t)img_local * s.elems;
+  const float lo0 = stats[z * 3].lo, hi0 = stats[z * 3].hi, lo1 = stats[z * 3 + 1].lo, hi1 = stats[z * 3 + 1].hi,
+              lo2 = stats[z * 3 + 2].lo, hi2 = stats[z * 3 + 2].hi;
+  const uint64_t npix = (uint64_t)s.h * s.w;
+  for (uint64_t p4 = (uint64_t)blockIdx.x * 256 + threadIdx.x; p4 * 4 < npix; p4 += (uint64_t)gridDim.x * 256) {
+    uint32_t o[12];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint64_t pix = min(p4 * 4 + k, npix - 1);
+      // inner (per-channel) denoise_wavelet clips to the normalised [0, 1] = [min, max] of the channel
+      const float y = fminf(fmaxf(base[g.off_plane + pix], lo0), hi0) - 16.0f;
+      const float cb = fminf(fmaxf(base[g.chan_floats + g.off_plane + pix], lo1), hi1) - 128.0f;
+      const float cr = fminf(fmaxf(base[2 * g.chan_floats + g.off_plane + pix], lo2), hi2) - 128.0f;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        float v = fa.inv[c][0] * y + fa.inv[c][1] * cb + fa.inv[c][2] * cr;
+        v = fminf(fmaxf(v, 0.0f), 1.0f);
+        o[3 * k + c] = (uint32_t)__float2int_rz(255.0f * v);
+      }
+    }
+    uint8_t* op = out + p4 * 12;
+    if (p4 * 4 + 4 <= npix && (reinterpret_cast<uintptr_t>(op) & 3u) == 0) {
+      uint32_t* ow = reinterpret_cast<uint32_t*>(op);
+      ow[0] = pack4(o[0], o[1], o[2], o[3]);
+      ow[1] = pack4(o[4], o[5], o[6], o[7]);
+      ow[2] = pack4(o[8], o[9], o[10], o[11]);
+    } else {
+      for (int k = 0; k < 12 && p4 * 12 + k < s.elems; ++k) op[k] = (uint8_t)o[k];
+    }
+  }
+}
+
+__global__ void k_wv_init(WvStats* stats, int nplanes) {
+  const int z = blockIdx.x * blockDim.x + threadIdx.x;
+  if (z >= nplanes) return;
+  WvStats& st = stats[z];
+  st.mn_ord = 0x7fffffff;
+  st.mx_ord = (int)0x80000000;
+  for (int l = 0; l <= WV_MAXL; ++l)
+    for (int b = 0; b < 3; ++b) { st.energy[l][b] = 0.0; st.thr[l][b] = 0.f; }
+  st.prefix[0] = st.prefix[1] = 0u;
+  st.rank[0] = st.rank[1] = 0ull;
+  st.count = 0ull;
+  st.sigma = 0.f;
+}
+
+// ------------------------------------------------------------------ host side
+constexpr size_t WV_BUDGET = 6ull << 30;           // workspace cap: images are processed in chunks
+
+static int wv_chunk(const WvGeom& g, int n) {
+  const size_t per_img = 3 * g.chan_floats * sizeof(float);
+  return (int)std::max<size_t>(1, std::min<size_t>((size_t)n, WV_BUDGET / std::max<size_t>(per_img, 1)));
+}
+
+size_t wavelet_workspace_bytes(const b2d_plan& p) {
+  size_t need = 0;
+  for (const SpecGroup& grp : p.groups) {
+    if (grp.spec.denoise != B2D_DENOISE_WAVELET) continue;
+    WvGeom g;
+    wavelet_geometry(g, grp.spec.wavelet, grp.spec.levels, p.h, p.w);
+    const int chunk = wv_chunk(g, (int)grp.images.size());
+    const size_t bytes = (size_t)chunk * 3 * (g.chan_floats * sizeof(float) + sizeof(WvStats) +
+                                              2 * WV_BINS * sizeof(unsigned int)) + 1024;
+    need = std::max(need, bytes);
+  }
+  return need;
+}
+
+template <int KIND>
+static void launch_color(int mode, dim3 grid, cudaStream_t st, const ImageSet& s, const NoiseArgs& na, const WvGeom& g,
+                         float* ws, WvStats* stats, int first) {
+  if (mode == NM_INJECT) k_wv_color<KIND, NM_INJECT><<<grid, 256, 0, st>>>(s, na, g, ws, stats, first);
+  else k_wv_color<KIND, NM_GEN><<<grid, 256, 0, st>>>(s, na, g, ws, stats, first);
+}
+
+static void invert3(const double m[3][3], double o[3][3]) {
+  const double det = m[0][0] * (m[1][1] * m[2][2] - m[1][2] * m[2][1]) - m[0][1] * (m[1][0] * m[2][2] - m[1][2] * m[2][0]) +
+                     m[0][2] * (m[1][0] * m[2][1] - m[1][1] * m[2][0]);
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) {
+      const int a = (j + 1) % 3, b = (j + 2) % 3, c = (i + 1) % 3, d = (i + 2) % 3;
+      o[i][j] = (m[a][c] * m[b][d] - m[a][d] * m[b][c]) / det;
+    }
+}
+
+int run_wavelet(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, int kind, int mode, const NoiseArgs& na,
+                uint8_t* ws8, cudaStream_t st) {
+  WvGeom g;
+  wavelet_geometry(g, sp.wavelet, sp.levels, p.h, p.w);
+  const int chunk = wv_chunk(g, s.count);
+  uint8_t* wbase = ws8 + p.off_denoise + (p.ws_bytes - p.off_denoise - wavelet_workspace_bytes(p));
+  float* ws = reinterpret_cast<float*>(wbase);
+  WvStats* stats = reinterpret_cast<WvStats*>(wbase + (size_t)chunk * 3 * g.chan_floats * sizeof(float));
+  unsigned int* hist = reinterpret_cast<unsigned int*>(reinterpret_cast<uint8_t*>(stats) + (size_t)chunk * 3 * sizeof(WvStats));
+  const double M[3][3] = {{65.481, 128.553, 24.966}, {-37.797, -74.203, 112.0}, {112.0, -93.786, -18.214}};
+  double inv[3][3];
+  invert3(M, inv);
+  WvFinalArgs fa;
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) fa.inv[i][j] = (float)inv[i][j];
+  auto blocks = [](size_t n) { return (unsigned)std::min<size_t>((n + 255) / 256, 148 * 8); };
+
+  for (int first = 0; first < s.count; first += chunk) {
+    const int cnt = std::min(chunk, s.count - first);
+    const int planes = cnt * 3;
+    k_wv_init<<<(planes + 127) / 128, 128, 0, st>>>(stats, planes);
+    cudaMemsetAsync(hist, 0, (size_t)planes * 2 * WV_BINS * sizeof(unsigned int), st);
+    const dim3 cgrid(blocks(((size_t)p.h * p.w + 7) / 8), 1, cnt);
+    switch (kind) {
+      case NK_NONE: launch_color<NK_NONE>(mode, cgrid, st, s, na, g, ws, stats, first); break;
+      case NK_GAUSSIAN: launch_color<NK_GAUSSIAN>(mode, cgrid, st, s, na, g, ws, stats, first); break;
+      case NK_SPECKLE: launch_color<NK_SPECKLE>(mode, cgrid, st, s, na, g, ws, stats, first); break;
+      case NK_SAP: launch_color<NK_SAP>(mode, cgrid, st, s, na, g, ws, stats, first); break;
+      case NK_POISSON: launch_color<NK_POISSON>(mode, cgrid, st, s, na, g, ws, stats, first); break;
+      case NK_UNIFORM: launch_color<NK_UNIFORM>(mode, cgrid, st, s, na, g, ws, stats, first); break;
+      case NK_RAYLEIGH: launch_color<NK_RAYLEIGH>(mode, cgrid, st, s, na, g, ws, stats, first); break;
+      case NK_GAMMA: launch_color<NK_GAMMA>(mode, cgrid, st, s, na, g, ws, stats, first); break;
+      case NK_TABLE_ADD: launch_color<NK_TABLE_ADD>(mode, cgrid, st, s, na, g, ws, stats, first); break;
+      case NK_SHADER: launch_color<NK_SHADER>(mode, cgrid, st, s, na, g, ws, stats, first); break;
+      default: return fail(B2D_ERR_INVALID, "wavelet: bad noise operator %d", kind);
+    }
+    count_launch();
+    for (int l = 1; l <= g.L; ++l) {
+      k_dwt_rows<<<dim3(blocks((size_t)g.h[l - 1] * g.w[l]), 1, planes), 256, 0, st>>>(
+          g, ws, l, l == 1 ? g.off_plane : g.off_app[l - 1]);
+      k_dwt_cols<<<dim3(blocks((size_t)g.h[l] * g.w[l]), 1, planes), 256, 0, st>>>(g, ws, l);
+      k_band_energy<<<dim3(std::min(blocks((size_t)g.h[l] * g.w[l]), 64u), 1, planes), 256, 0, st>>>(g, ws, stats, l);
+      count_launch(); count_launch(); count_launch();
+    }
+    for (int pass = 0; pass < 3; ++pass) {
+      k_select_hist<<<dim3(std::min(blocks((size_t)g.h[1] * g.w[1]), 32u), 1, planes), 256, 0, st>>>(g, ws, stats, hist, pass);
+      k_select_step<<<(planes + 63) / 64, 64, 0, st>>>(stats, hist, pass, planes);
+      count_launch(); count_launch();
+    }
+    k_thresholds<<<(planes + 63) / 64, 64, 0, st>>>(g, stats, planes);
+    count_launch();
+    for (int l = g.L; l >= 1; --l) {
+      k_idwt_rows<<<dim3(blocks((size_t)g.h[l] * g.w[l - 1]), 1, planes), 256, 0, st>>>(g, ws, stats, l);
+      k_idwt_cols<<<dim3(blocks((size_t)g.h[l - 1] * g.w[l - 1]), 1, planes), 256, 0, st>>>(g, ws, l);
+      count_launch(); count_launch();
+    }
+    k_wv_final<<<dim3(blocks(((size_t)p.h * p.w + 3) / 4), 1, cnt), 256, 0, st>>>(s, g, ws, stats, fa, first);
+    count_launch();
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail_cuda(e, "wavelet launch");
+  }
+  return B2D_OK;
+}
+
+}  // namespace b2d

@@ -1,0 +1,34 @@
+// b2d_wavelet.cuh - geometry / statistics records of the wavelet denoiser.
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+namespace b2d {
+
+constexpr int WV_MAXL = 8;      // levels
+constexpr int WV_MAXF = 10;     // filter taps (bior1.5)
+constexpr int WV_BINS = 2048;   // radix-select histogram bins per pass
+
+struct WvGeom {
+  int F, L;
+  int h[WV_MAXL + 1], w[WV_MAXL + 1];           // band sizes per level; [0] = image
+  float dec_lo[WV_MAXF], dec_hi[WV_MAXF], rec_lo[WV_MAXF], rec_hi[WV_MAXF];
+  // float offsets inside one channel's workspace block
+  size_t off_plane, off_tlo, off_thi, off_app[WV_MAXL + 1], off_det[WV_MAXL + 1][3];
+  size_t chan_floats;
+};
+
+struct WvStats {                 // one per (image in chunk, channel)
+  int mn_ord, mx_ord;            // ordered-int min / max of the channel
+  double energy[WV_MAXL + 1][3]; // sum d^2 per level / band (0: 'da', 1: 'ad', 2: 'dd')
+  unsigned int prefix[2];        // radix select state for ranks (n-1)/2 and n/2
+  unsigned long long rank[2];
+  unsigned long long count;      // non-zero |dd_1| coefficients
+  float sigma;
+  float thr[WV_MAXL + 1][3];
+  float lo, hi;                  // clip range = channel min / max
+};
+
+void wavelet_geometry(WvGeom& g, int wavelet, int levels_req, int h, int w);
+
+}  // namespace b2d
