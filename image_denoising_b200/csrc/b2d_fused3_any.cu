@@ -1,4 +1,5 @@
-// b2d_fused3.cu - noise -> ->u8 -> 3x3 denoiser in ONE pass over HBM.
+// b2d_fused3.cu - noise -> ->u8 -> 3x3 denoiser in ONE pass over HBM: the GENERAL variant
+// (rows that are a multiple of 4 but not of 8 bytes); the hot variant is b2d_fused3w.cu.
 //
 // Replaces, per image, e.g.
 //     gauss_array = random_noise(img, mode='gaussian', var=v)
@@ -51,7 +52,7 @@ __device__ __forceinline__ uint2 load_group(const uint8_t* img, uint64_t elems, 
 }
 
 template <int KIND, int FILTER>
-__global__ void __launch_bounds__(F3_THREADS) k_fused3(ImageSet s, NoiseArgs na) {
+__global__ void __launch_bounds__(F3_THREADS) k_fused3_any(ImageSet s, NoiseArgs na) {
   using F = Filter3<FILTER>;
   using Nz = NoiseOp<KIND, NM_GEN>;
   extern __shared__ __align__(16) uint8_t smem[];
@@ -128,7 +129,7 @@ template <int KIND, int FILTER>
 static cudaError_t launch_one(const ImageSet& s, const NoiseArgs& na, cudaStream_t st) {
   const dim3 grid((s.rowbytes + F3_TILE_WB - 1) / F3_TILE_WB, (s.h + F3_TILE_H - 1) / F3_TILE_H, s.count);
   const size_t smem = (size_t)F3_ROWS * F3_SROW;
-  k_fused3<KIND, FILTER><<<grid, F3_THREADS, smem, st>>>(s, na);
+  k_fused3_any<KIND, FILTER><<<grid, F3_THREADS, smem, st>>>(s, na);
   count_launch();
   return cudaGetLastError();
 }
@@ -143,7 +144,7 @@ static cudaError_t launch_filter(int filter, const ImageSet& s, const NoiseArgs&
   return cudaErrorInvalidValue;
 }
 
-cudaError_t launch_fused3(int kind, int filter, const ImageSet& s, const NoiseArgs& na, cudaStream_t st) {
+cudaError_t launch_fused3_any(int kind, int filter, const ImageSet& s, const NoiseArgs& na, cudaStream_t st) {
   if (s.count <= 0) return cudaSuccess;
   switch (kind) {
     case NK_NONE: return launch_filter<NK_NONE>(filter, s, na, st);

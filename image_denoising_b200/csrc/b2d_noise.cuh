@@ -68,6 +68,32 @@ __device__ __forceinline__ bool in_image(const NoiseArgs& a, const GroupCtx& g, 
 
 // ---- gaussian: clip(f + N(0, sqrt(var)), 0, 1) ->u8  (minibatch.py:117-118)
 // ---- speckle:  clip(f + f * N(0, sqrt(var)), 0, 1)   (minibatch.py:380-383)
+// Two N(0, sigma^2) samples from one 32-bit Philox word (Box-Muller on two 16-bit
+// uniforms).  Integer -> float goes through the 2^23 magic number (PRMT + FADD): I2F.U16
+// and F2I are quarter-rate XU-pipe instructions on sm_100a (scripts/ubench/pipes.cu).
+//   u1 = (ka + 0.5) / 65536, theta = 2 pi (kb + 0.5) / 65536
+//   n  = sigma * sqrt(-2 ln u1) * (cos, sin)(theta);   sigma^2 is folded into the sqrt argument
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+  uint32_t d;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+  return d;
+}
+#define B2D_MAGIC 0x4B000000u   /* 2^23 as fp32 bits: 0x4B0000xx == 8388608 + xx */
+__device__ __forceinline__ float magic_lo16(uint32_t w) { return __uint_as_float(prmt(w, B2D_MAGIC, 0x7410u)); }
+__device__ __forceinline__ float magic_hi16(uint32_t w) { return __uint_as_float(prmt(w, B2D_MAGIC, 0x7432u)); }
+template <int I>
+__device__ __forceinline__ float magic_byte(uint32_t w) { return __uint_as_float(prmt(w, B2D_MAGIC, 0x7440u | I)); }
+
+__device__ __forceinline__ void normal_pair(uint32_t r32, float sigma, float& n0, float& n1) {
+  const float a = magic_lo16(r32) - 8388607.5f;                       // ka + 0.5, exact
+  const float kb = magic_hi16(r32) - 8388608.0f;                      // exact
+  const float s2 = sigma * sigma * 1.3862943611198906f;               // sigma^2 * 2 ln 2 (loop invariant)
+  const float rad = fast_sqrt(fmaf(fast_lg2(a), -s2, 16.0f * s2));    // sigma * sqrt(-2 ln u1)
+  const float th = fmaf(kb, 6.283185307179586f / 65536.0f, 3.141592653589793f / 65536.0f);
+  n0 = rad * fast_cos(th);
+  n1 = rad * fast_sin(th);
+}
+
 template <int MODE, bool SPECKLE>
 struct NormalNoise {
   static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8],
@@ -86,18 +112,20 @@ struct NormalNoise {
       return;
     }
     const uint4 r = group_random(a, g, 0);
+    const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      float z0, z1;
-      box_muller16(r16(r, 2 * j), r16(r, 2 * j + 1), z0, z1);
-      const float n0 = a.p0 * z0, n1 = a.p0 * z1;
+      float n0, n1;
+      normal_pair(rw[j], a.p0, n0, n1);
       if (MODE == NM_DUMP) {
         if (in_image(a, g, 2 * j)) a.dump0[field_index(a, g, 2 * j)] = n0;
         if (in_image(a, g, 2 * j + 1)) a.dump0[field_index(a, g, 2 * j + 1)] = n1;
       }
+      // exact v + 255 n (or v + v n), one rounding toward zero; the packed operator below
+      // truncates the same exact value, so both agree on the uint8 result
       const float v0 = (float)v[2 * j], v1 = (float)v[2 * j + 1];
-      const float x0 = SPECKLE ? fmaf(v0, n0, v0) : fmaf(n0, 255.0f, v0);
-      const float x1 = SPECKLE ? fmaf(v1, n1, v1) : fmaf(n1, 255.0f, v1);
+      const float x0 = SPECKLE ? __fmaf_rz(v0, n0, v0) : __fmaf_rz(n0, 255.0f, v0);
+      const float x1 = SPECKLE ? __fmaf_rz(v1, n1, v1) : __fmaf_rz(n1, 255.0f, v1);
       const float c0 = fminf(fmaxf(x0, 0.0f), 255.0f), c1 = fminf(fmaxf(x1, 0.0f), 255.0f);
       if (xf) { xf[2 * j] = c0; xf[2 * j + 1] = c1; }
       v[2 * j] = (uint32_t)__float2int_rz(c0);
@@ -109,7 +137,7 @@ template <int MODE> struct NoiseOp<NK_GAUSSIAN, MODE> : NormalNoise<MODE, false>
 template <int MODE> struct NoiseOp<NK_SPECKLE, MODE> : NormalNoise<MODE, true> {};
 
 // ---- s&p: flipped = u1 < amount; salted = u2 < 0.5   (minibatch.py:259)
-// generator: 15 bits decide the flip, 1 bit salt/pepper.
+// generator: the low 15 bits of a 16-bit draw decide the flip, bit 15 salt/pepper.
 template <int MODE>
 struct NoiseOp<NK_SAP, MODE> {
   static __device__ __forceinline__ void apply8(const NoiseArgs& a, const GroupCtx& g, uint32_t (&v)[8],
@@ -127,10 +155,10 @@ struct NoiseOp<NK_SAP, MODE> {
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const uint32_t k = r16(r, i);
-      const bool flip = (k >> 1) < a.u0;
-      const bool salt = (k & 1u) != 0u;
+      const bool flip = (k & 0x7fffu) < a.u0;
+      const bool salt = (k & 0x8000u) != 0u;
       if (MODE == NM_DUMP && in_image(a, g, i)) {
-        a.dump0[field_index(a, g, i)] = ((float)(k >> 1) + 0.5f) * (1.0f / 32768.0f);
+        a.dump0[field_index(a, g, i)] = ((float)(k & 0x7fffu) + 0.5f) * (1.0f / 32768.0f);
         a.dump1[field_index(a, g, i)] = salt ? 0.25f : 0.75f;
       }
       v[i] = flip ? (salt ? 255u : 0u) : v[i];
@@ -396,5 +424,87 @@ __device__ __forceinline__ void apply8_float(const NoiseArgs& a, const GroupCtx&
     for (int i = 0; i < 8; ++i) xf[i] = (float)v[i];
   }
 }
+
+
+// ===========================================================================
+// Packed operators: one 8-byte group held as two 32-bit words, never unpacked
+// to one register per byte.  These are what the fused kernels and the
+// noise-only kernel run in generator mode; they compute exactly the uint8
+// values of the unpacked operators above (tests/test_gpu_filters3.py compares
+// the two paths).  Cost model (scripts/ubench/pipes.cu, cycles per warp
+// instruction per SM sub-partition): ALU-class 2, IMAD 2, IMAD.WIDE 4, FFMA 1,
+// MUFU / F2I 8; one Philox4x32-10 block = 20 IMAD.WIDE + 20 LOP3.
+// ===========================================================================
+template <int KIND>
+struct PackedNoise {                 // default: unpack -> per-element operator -> pack
+  static constexpr bool kNative = false;
+  static __device__ __forceinline__ uint2 apply(const NoiseArgs& a, const GroupCtx& g, uint2 w) {
+    uint32_t v[8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[i] = byte_of(w.x, i);
+      v[4 + i] = byte_of(w.y, i);
+    }
+    NoiseOp<KIND, NM_GEN>::apply8(a, g, v);
+    return make_uint2(pack4(v[0], v[1], v[2], v[3]), pack4(v[4], v[5], v[6], v[7]));
+  }
+};
+
+template <>
+struct PackedNoise<NK_NONE> {
+  static constexpr bool kNative = true;
+  static __device__ __forceinline__ uint2 apply(const NoiseArgs&, const GroupCtx&, uint2 w) { return w; }
+};
+
+// s&p on bytes: per 16-bit draw k, lane = 0x8000 + (k & 0x7fff) - T has bit 15 clear iff
+// the element flips; PRMT's sign-replicate mode turns bits 15 of four lanes into a
+// byte mask, one LOP3 selects {value, 255, 0}.  7 ALU instructions per 4 bytes.
+template <>
+struct PackedNoise<NK_SAP> {
+  static constexpr bool kNative = true;
+  static __device__ __forceinline__ uint2 apply(const NoiseArgs& a, const GroupCtx& g, uint2 w) {
+    const uint4 r = group_random(a, g, 0);
+    const uint32_t tt = a.u0 * 0x00010001u;
+    const uint32_t y0 = (r.x | 0x80008000u) - tt, y1 = (r.y | 0x80008000u) - tt;
+    const uint32_t y2 = (r.z | 0x80008000u) - tt, y3 = (r.w | 0x80008000u) - tt;
+    const uint32_t keep0 = prmt(y0, y1, 0xFDB9u), keep1 = prmt(y2, y3, 0xFDB9u);   // 0xff: no flip
+    const uint32_t salt0 = prmt(r.x, r.y, 0xFDB9u), salt1 = prmt(r.z, r.w, 0xFDB9u);
+    return make_uint2((w.x & keep0) | (~keep0 & salt0), (w.y & keep1) | (~keep1 & salt1));
+  }
+};
+
+// gaussian / speckle: x = v + 255 n (v + v n) evaluated exactly by one FFMA.RZ onto the
+// magic number 2^23 + v, so the low 16 bits of the result are floor(x) as a signed
+// 16-bit integer (x < 0 lands below 2^23 where the spacing is 0.5: still negative);
+// VIMNMX.S16x2.RELU clamps two elements to [0, 255] in one instruction.
+// Needs |x| < 16384: b2d_plan_create bounds var for these two noises.
+template <bool SPECKLE>
+struct PackedNormal {
+  static constexpr bool kNative = true;
+  template <int I>
+  static __device__ __forceinline__ uint32_t elem(uint32_t w, float n) {
+    const float mv = magic_byte<I>(w);
+    const float t = SPECKLE ? __fmaf_rz(mv - 8388608.0f, n, mv) : __fmaf_rz(n, 255.0f, mv);
+    return __float_as_uint(t);
+  }
+  static __device__ __forceinline__ uint32_t clamp2(uint32_t t0, uint32_t t1) {
+    return __vimin_s16x2_relu(prmt(t0, t1, 0x5410u), 0x00ff00ffu);
+  }
+  static __device__ __forceinline__ uint2 apply(const NoiseArgs& a, const GroupCtx& g, uint2 w) {
+    const uint4 r = group_random(a, g, 0);
+    float n0, n1, n2, n3, n4, n5, n6, n7;
+    normal_pair(r.x, a.p0, n0, n1);
+    normal_pair(r.y, a.p0, n2, n3);
+    normal_pair(r.z, a.p0, n4, n5);
+    normal_pair(r.w, a.p0, n6, n7);
+    const uint32_t l01 = clamp2(elem<0>(w.x, n0), elem<1>(w.x, n1));
+    const uint32_t l23 = clamp2(elem<2>(w.x, n2), elem<3>(w.x, n3));
+    const uint32_t l45 = clamp2(elem<0>(w.y, n4), elem<1>(w.y, n5));
+    const uint32_t l67 = clamp2(elem<2>(w.y, n6), elem<3>(w.y, n7));
+    return make_uint2(prmt(l01, l23, 0x6420u), prmt(l45, l67, 0x6420u));
+  }
+};
+template <> struct PackedNoise<NK_GAUSSIAN> : PackedNormal<false> {};
+template <> struct PackedNoise<NK_SPECKLE> : PackedNormal<true> {};
 
 }  // namespace b2d

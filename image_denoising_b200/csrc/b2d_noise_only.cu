@@ -47,7 +47,18 @@ __global__ void __launch_bounds__(NO_THREADS) k_noise_only(ImageSet s, NoiseArgs
     uint32_t v[8];
     load_group_any(img, s.elems, g, v);
     GroupCtx gc{(uint32_t)img_local, g, img};
-    NoiseOp<KIND, MODE>::apply8(na, gc, v);
+    if (MODE == NM_GEN) {
+      // generator mode runs the packed operators, the same code the fused kernels run
+      const uint2 w = PackedNoise<KIND>::apply(
+          na, gc, make_uint2(pack4(v[0], v[1], v[2], v[3]), pack4(v[4], v[5], v[6], v[7])));
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        v[i] = byte_of(w.x, i);
+        v[4 + i] = byte_of(w.y, i);
+      }
+    } else {
+      NoiseOp<KIND, MODE>::apply8(na, gc, v);
+    }
     if (MODE != NM_DUMP) store_group_any(out, s.elems, g, v);
   }
 }

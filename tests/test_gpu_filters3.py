@@ -10,7 +10,9 @@ from oracle import denoise as D
 pytestmark = pytest.mark.gpu
 
 SHAPES = [(64, 96), (600, 1000), (375, 500), (33, 344), (32, 256), (31, 260), (1, 4), (2, 8), (5, 1), (3, 2),
-          (37, 53), (70, 342), (129, 1027)]
+          (37, 53), (70, 342), (129, 1027),
+          # fast tiled path (W % 8 == 0): multi-tile widths, row end on / next to a tile boundary, short bands
+          (130, 2048), (65, 1368), (200, 8), (67, 1024), (3, 1032), (128, 344)]
 ORACLE = {"gaus_blur": D.gaus_blur_cv2, "mean": D.mean_cv2, "median": lambda u: D.median_cv2(u, 3)}
 
 
@@ -30,3 +32,18 @@ def test_filter3_bit_exact(cuda, shape, den):
 def test_mean_divider_exhaustive():
     s = np.arange(0, 9 * 255 + 1)
     assert np.array_equal(((s + 4) * 7282) >> 16, (2 * s + 9) // 18)
+
+
+@pytest.mark.parametrize("shape", [(64, 96), (131, 1368), (600, 1000), (37, 53)])
+@pytest.mark.parametrize("noise", ["gaussian_%s_var1.5", "speckle_%s_var1.0", "sap_%s_var0.4", "uniform_%s_var0.6",
+                                   "poisson_%s", "periodic_%s_var100", "rayleigh_%s_var0.2"])
+@pytest.mark.parametrize("den", ["gaus_blur", "mean", "median"])
+def test_fused_equals_two_pass(cuda, shape, noise, den):
+    """One-pass fused kernel (packed generator in the prologue) == noise pass then filter pass."""
+    from image_denoising_b200 import api
+    h, w = shape
+    batch = torch.from_numpy(synth_batch(3, h, w, seed=h + w, kind="smooth")).to(cuda)
+    fused = api.apply(batch, noise % den, seed=11, first_index=7)
+    noisy = api.apply(batch, (noise % "x").replace("_x", ""), seed=11, first_index=7)
+    two = api.apply(noisy, "original_" + den)
+    assert torch.equal(fused, two), (shape, noise, den, int((fused != two).sum()))
