@@ -9,7 +9,7 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200denoise.so")
+LIB_PATH = os.environ.get("B2D_LIB") or os.path.join(_HERE, "libb200denoise.so")   # B2D_LIB: kernel-tuning variants
 CSRC = os.path.join(_HERE, "csrc")
 
 OK, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_PARSE, ERR_NO_DEVICE = 0, -1, -2, -3, -4, -5

@@ -23,7 +23,14 @@ namespace b2d {
 
 constexpr int FT_THREADS = 256;
 constexpr int FT_TWB = 1024;               // tile width in bytes
-constexpr int FT_TH = 64;                  // tile height in rows
+#ifndef B2D_FT_TH
+#define B2D_FT_TH 48
+#endif
+#ifndef B2D_FT_UNROLL
+#define B2D_FT_UNROLL 4
+#endif
+constexpr int FT_UNROLL = B2D_FT_UNROLL;
+constexpr int FT_TH = B2D_FT_TH;           // tile height in rows (48: 4 CTAs / SM by shared memory and registers)
 constexpr int FT_APRON = 16;               // bytes each side in shared memory (8 are used)
 constexpr int FT_SROW = FT_TWB + 2 * FT_APRON;
 constexpr int FT_ROWS = FT_TH + 2;
@@ -37,7 +44,7 @@ __device__ __forceinline__ uint2 noise_group(const NoiseArgs& na, int img_local,
 }
 
 template <int KIND, int FILTER, int KW>
-__global__ void __launch_bounds__(FT_THREADS) k_fused3(ImageSet s, NoiseArgs na) {
+__global__ void __launch_bounds__(FT_THREADS, 4) k_fused3(ImageSet s, NoiseArgs na) {
   using F = Filter3W<FILTER, KW>;
   constexpr int TPB = FT_TWB / (4 * KW);            // threads per band
   constexpr int BANDS = FT_THREADS / TPB;
@@ -57,7 +64,7 @@ __global__ void __launch_bounds__(FT_THREADS) k_fused3(ImageSet s, NoiseArgs na)
     const int c = c0 + 16 * q;
     const bool v0 = c < s.rowbytes, v1 = c + 8 < s.rowbytes;
     if (v0) {
-#pragma unroll 2
+#pragma unroll FT_UNROLL
       for (int tr = r0; tr < rows; tr += 4) {
         const int ys = border_map(y0 - 1 + tr, s.h, F::BORDER);
         const uint32_t e = (uint32_t)ys * (uint32_t)s.rowbytes + (uint32_t)c;
