@@ -150,3 +150,15 @@ def corrupt(im, noise, seed=DEFAULT_SEED, index=0, side="test", rng=None, **over
     spec = resolve_mix(noise, side, rng)
     im = np.ascontiguousarray(im)
     return corrupt_host(im[None], spec, seed, index, **overrides)[0]
+
+
+def lab_convert(pixels, direction):
+    """Test hook (b2d_lab_convert): (..., 3) uint8 device tensor, 0 = BGR->Lab, 1 = Lab->BGR."""
+    if pixels.dtype != torch.uint8 or not pixels.is_cuda or not pixels.is_contiguous() or pixels.shape[-1] != 3:
+        raise ValueError("pixels must be a contiguous uint8 CUDA tensor of shape (..., 3)")
+    out = torch.empty_like(pixels)
+    stream = torch.cuda.current_stream(pixels.device).cuda_stream
+    with torch.cuda.device(pixels.device):
+        _lib.check(_lib.lib().b2d_lab_convert(pixels.data_ptr(), out.data_ptr(), pixels.numel() // 3, int(direction),
+                                              stream))
+    return out

@@ -4,6 +4,7 @@
 #pragma once
 #include "b2d_kernels.cuh"
 #include "../../include/b200denoise.h"
+#include "b2d_plan.h"
 
 namespace b2d {
 
@@ -18,9 +19,14 @@ cudaError_t launch_filter3_bytes(int filter, const ImageSet& s, cudaStream_t st)
 namespace b2d {
 // median 5/7, bilateral (uint8 in -> uint8 out, already noised)
 int run_denoise_pass(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, uint8_t* ws, cudaStream_t st);
-// quant / bloom: pixel-granular corruption written as a uint8 image
-int run_pixel_noise(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, uint8_t* ws, const b2d_fields* fields,
-                    uint64_t seed, uint64_t first_global, cudaStream_t st);
+// quant / bloom: pixel-granular corruption written as a uint8 image (s.out); `tables` = plan scratch
+size_t quant_table_bytes(int n);
+size_t bloom_table_bytes(int n, int h);
+int run_quant(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, uint8_t* tables, const b2d_fields* fields,
+              uint64_t seed, uint64_t first_global, cudaStream_t st);
+int run_bloom(const b2d_plan& p, const ImageSet& s, const SpecGroup& g, int lo, int hi, uint8_t* tables,
+              const b2d_fields* fields, uint64_t seed, uint64_t first_global, cudaStream_t st);
+cudaError_t launch_lab_convert(const uint8_t* in, uint8_t* out, size_t n, int dir, cudaStream_t st);
 // noise (operator `kind`, float where the reference keeps float) -> BayesShrink wavelet -> ->u8
 int run_wavelet(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, int kind, int mode, const NoiseArgs& na,
                 uint8_t* ws, cudaStream_t st);

@@ -122,7 +122,10 @@ int run_group(const RunCtx& c, const SpecGroup& g, int lo, int hi) {
       uint8_t* dst = sp.denoise == B2D_DENOISE_NONE ? c.out : stage;
       ImageSet ps = s;
       ps.out = dst;
-      const int rc = run_pixel_noise(*p, sp, ps, c.ws, c.fields, c.seed, c.first_global, c.st);
+      uint8_t* tables = c.ws + p->off_pix;
+      const int rc = sp.noise == B2D_NOISE_QUANT
+                         ? run_quant(*p, sp, ps, tables, c.fields, c.seed, c.first_global, c.st)
+                         : run_bloom(*p, ps, g, lo, hi, tables, c.fields, c.seed, c.first_global, c.st);
       if (rc) return rc;
       if (sp.denoise == B2D_DENOISE_NONE) return B2D_OK;
       ImageSet ds = s;
@@ -250,5 +253,16 @@ extern "C" int b2d_noise_field(b2d_plan* plan, float* d_f0, float* d_f1, uint64_
     ImageSet s = make_set(plan, reinterpret_cast<const uint8_t*>(d_f0), nullptr, g, 0, (int)g.images.size());
     CK(launch_noise_only(kind, NM_DUMP, s, na, st));
   }
+  return B2D_OK;
+}
+
+// ---------------------------------------------------------------------------
+// test hook: the 8-bit Lab conversions of the quant branch
+// ---------------------------------------------------------------------------
+extern "C" int b2d_lab_convert(const uint8_t* d_in, uint8_t* d_out, size_t n_pixels, int direction, void* cuda_stream) {
+  if (!d_in || !d_out) return fail(B2D_ERR_INVALID, "b2d_lab_convert: null argument");
+  if (direction != 0 && direction != 1) return fail(B2D_ERR_INVALID, "b2d_lab_convert: direction must be 0 or 1");
+  if (n_pixels == 0) return B2D_OK;
+  CK(launch_lab_convert(d_in, d_out, n_pixels, direction, static_cast<cudaStream_t>(cuda_stream)));
   return B2D_OK;
 }

@@ -30,7 +30,7 @@ struct b2d_plan {
   std::vector<b2d::SpecGroup> groups;
   std::vector<b2d::PeriodicTable> periodic;
   // workspace layout (byte offsets into the caller's d_ws)
-  size_t ws_bytes, off_par, off_bitmap, off_stage, off_aux, off_scan, off_denoise;
+  size_t ws_bytes, off_par, off_bitmap, off_stage, off_aux, off_scan, off_denoise, off_pix;
   uint32_t brown_chunks;
   bool need_aux;
   // b2d_run_host resources (lazily created)

@@ -1,0 +1,252 @@
+// b2d_quant.cu - `quant`: colour quantisation in Lab (lib/roi_data_layer/minibatch.py:496-507)
+//     image = cv2.cvtColor(img, cv2.COLOR_BGR2LAB); image = image.reshape((h * w, 3))
+//     clt = MiniBatchKMeans(n_clusters=k); labels = clt.fit_predict(image)
+//     quant = clt.cluster_centers_.astype("uint8")[labels]
+//     quant = cv2.cvtColor(quant.reshape((h, w, 3)), cv2.COLOR_LAB2BGR)
+//
+//   k_quant_fit     one CTA per image: k-means++ seeding + Lloyd iterations on a Philox-chosen
+//                   sample of pixels (distribution-level stand-in for MiniBatchKMeans.fit, whose
+//                   result depends on the sklearn version and its RNG - SURVEY 7.2 item 7);
+//                   skipped when the float64 centres are injected;
+//   k_quant_palette centres.astype(uint8) -> Lab -> BGR for the k palette entries;
+//   k_quant_apply   BGR -> Lab (OpenCV's 8-bit fixed-point path, tables in b2d_lab_tables.h),
+//                   label = argmin of the float64 squared distance in NumPy's operation order,
+//                   write the palette colour: 3 B read + 3 B written per pixel.
+// The two Lab conversions are bit-exact against cv2 over all 2^24 inputs (scripts/gen_lab_tables.py,
+// tests/test_gpu_quant.py).
+#include "b2d_denoise.cuh"
+#include "b2d_plan.h"
+
+#include <algorithm>
+
+#define B2D_LAB_TABLE __device__ const
+#include "b2d_lab_tables.h"
+
+namespace b2d {
+
+constexpr int QK_MAX = 32;            // validate_spec bounds k
+constexpr int Q_SAMPLES = 4096;       // pixels sampled per image for the fit
+constexpr int Q_ITERS = 16;
+
+__device__ __forceinline__ int descale(int x, int n) { return (x + (1 << (n - 1))) >> n; }
+__device__ __forceinline__ int clamp255(int v) { return min(max(v, 0), 255); }
+
+// RGB2Lab_b (cv2, uint8): src in B, G, R order.  gam / cb may point to shared copies of the tables.
+__device__ __forceinline__ uint32_t lab_forward(uint32_t b, uint32_t g, uint32_t r, const uint16_t* gam,
+                                                const uint16_t* cb) {
+  const int sb = gam[b], sg = gam[g], sr = gam[r];
+  const int fx = cb[descale(sb * kLabFwd[0] + sg * kLabFwd[1] + sr * kLabFwd[2], 12)];
+  const int fy = cb[descale(sb * kLabFwd[3] + sg * kLabFwd[4] + sr * kLabFwd[5], 12)];
+  const int fz = cb[descale(sb * kLabFwd[6] + sg * kLabFwd[7] + sr * kLabFwd[8], 12)];
+  const int L = clamp255(descale(296 * fy - 1336934, 15));
+  const int a = clamp255(descale(500 * (fx - fy) + 128 * 32768, 15));
+  const int bb = clamp255(descale(200 * (fy - fz) + 128 * 32768, 15));
+  return (uint32_t)L | ((uint32_t)a << 8) | ((uint32_t)bb << 16);
+}
+
+// abToXZ_b as a function (C integer division truncates toward zero, like the table's initialiser)
+__device__ __forceinline__ int ab_to_xz(int i) {
+  if (i <= 3390) return i * 108 / 841 - (1 << 14) * 16 / 116 * 108 / 841;
+  return i * i / (1 << 14) * i / (1 << 14);
+}
+
+// Lab2RGBinteger (cv2, uint8): returns B | G << 8 | R << 16
+__device__ __forceinline__ uint32_t lab_inverse(int L, int a, int b) {
+  const int y = kLabYF[2 * L], ify = kLabYF[2 * L + 1];
+  const int adiv = ((5 * a * 53687 + (1 << 7)) >> 13) - 128 * (1 << 14) / 500;
+  const int bdiv = ((b * 41943 + (1 << 4)) >> 9) - 128 * (1 << 14) / 200 + 1;
+  const int x = ab_to_xz(ify + adiv), z = ab_to_xz(ify - bdiv);
+  int c[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k)
+    c[k] = min(max(descale(kLabInv[3 * k] * x + kLabInv[3 * k + 1] * y + kLabInv[3 * k + 2] * z, 14), 0), 4095);
+  return (uint32_t)kLabInvGamma[c[2]] | ((uint32_t)kLabInvGamma[c[1]] << 8) | ((uint32_t)kLabInvGamma[c[0]] << 16);
+}
+
+__device__ __forceinline__ void stage_tables(uint16_t* s_gam, uint16_t* s_cb) {
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) s_gam[i] = kLabGamma[i];
+  for (int i = threadIdx.x; i < 3072; i += blockDim.x) s_cb[i] = kLabCbrt[i];
+  __syncthreads();
+}
+
+// ------------------------------------------------------------------ fit --
+__global__ void __launch_bounds__(256) k_quant_fit(ImageSet s, int k, uint32_t k0, uint32_t k1, uint64_t first_global,
+                                                   double* centres /* [batch][QK_MAX][3] */) {
+  __shared__ uint16_t s_gam[256], s_cb[3072];
+  __shared__ uint32_t smp[Q_SAMPLES];            // L | a << 8 | b << 16
+  __shared__ float mind[Q_SAMPLES];
+  __shared__ float cen[QK_MAX][3];
+  __shared__ unsigned int sums[QK_MAX][4];       // integer sums: deterministic accumulation
+  __shared__ float part[256];
+  stage_tables(s_gam, s_cb);
+  const int tid = threadIdx.x;
+  const int img_local = image_of(s, blockIdx.x);
+  const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
+  const uint64_t gi = first_global + (uint64_t)img_local;
+  const uint32_t npix = (uint32_t)(s.h * s.w);
+  for (int i = tid; i < Q_SAMPLES / 4; i += 256) {
+    const uint4 r = philox4x32_10((uint32_t)i, 0xC0u, (uint32_t)gi, (uint32_t)(gi >> 32), k0, k1);
+    const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t p = (uint32_t)(((uint64_t)rr[j] * npix) >> 32);
+      const uint8_t* px = img + (size_t)p * 3;
+      smp[4 * i + j] = lab_forward(px[0], px[1], px[2], s_gam, s_cb);
+    }
+  }
+  __syncthreads();
+  auto dist2 = [&](uint32_t v, int c) {
+    const float d0 = (float)(v & 255u) - cen[c][0], d1 = (float)((v >> 8) & 255u) - cen[c][1],
+                d2 = (float)((v >> 16) & 255u) - cen[c][2];
+    return d0 * d0 + d1 * d1 + d2 * d2;
+  };
+  // ---- k-means++ seeding: next centre drawn with probability proportional to min distance^2
+  const uint4 ru = philox4x32_10(0u, 0xC1u, (uint32_t)gi, (uint32_t)(gi >> 32), k0, k1);
+  if (tid == 0) {
+    const uint32_t v = smp[ru.x % Q_SAMPLES];
+    cen[0][0] = (float)(v & 255u); cen[0][1] = (float)((v >> 8) & 255u); cen[0][2] = (float)((v >> 16) & 255u);
+  }
+  for (int i = tid; i < Q_SAMPLES; i += 256) mind[i] = 3.0e38f;
+  __syncthreads();
+  for (int c = 1; c < k; ++c) {
+    float loc = 0.f;
+    for (int j = 0; j < Q_SAMPLES / 256; ++j) {          // thread owns a contiguous run of samples
+      const int i = tid * (Q_SAMPLES / 256) + j;
+      const float d = fminf(mind[i], dist2(smp[i], c - 1));
+      mind[i] = d;
+      loc += d;
+    }
+    part[tid] = loc;
+    __syncthreads();
+    if (tid == 0) {
+      float tot = 0.f;
+      for (int t = 0; t < 256; ++t) tot += part[t];
+      const uint4 rc = philox4x32_10((uint32_t)c, 0xC2u, (uint32_t)gi, (uint32_t)(gi >> 32), k0, k1);
+      float target = tot * ((float)(rc.x >> 8) * (1.0f / 16777216.0f));
+      int t = 0;
+      while (t < 255 && target >= part[t]) { target -= part[t]; ++t; }
+      int i = t * (Q_SAMPLES / 256);
+      const int end = i + Q_SAMPLES / 256 - 1;
+      while (i < end && target >= mind[i]) { target -= mind[i]; ++i; }
+      const uint32_t v = smp[i];
+      cen[c][0] = (float)(v & 255u); cen[c][1] = (float)((v >> 8) & 255u); cen[c][2] = (float)((v >> 16) & 255u);
+    }
+    __syncthreads();
+  }
+  // ---- Lloyd iterations on the sample
+  for (int it = 0; it < Q_ITERS; ++it) {
+    for (int i = tid; i < QK_MAX * 4; i += 256) (&sums[0][0])[i] = 0u;
+    __syncthreads();
+    for (int i = tid; i < Q_SAMPLES; i += 256) {
+      const uint32_t v = smp[i];
+      int best = 0;
+      float bd = dist2(v, 0);
+      for (int c = 1; c < k; ++c) {
+        const float d = dist2(v, c);
+        if (d < bd) { bd = d; best = c; }
+      }
+      atomicAdd(&sums[best][0], v & 255u);
+      atomicAdd(&sums[best][1], (v >> 8) & 255u);
+      atomicAdd(&sums[best][2], (v >> 16) & 255u);
+      atomicAdd(&sums[best][3], 1u);
+    }
+    __syncthreads();
+    if (tid < k && sums[tid][3]) {
+      const float inv = 1.0f / (float)sums[tid][3];
+      cen[tid][0] = (float)sums[tid][0] * inv; cen[tid][1] = (float)sums[tid][1] * inv; cen[tid][2] = (float)sums[tid][2] * inv;
+    }
+    __syncthreads();
+  }
+  if (tid < k) {
+    double* o = centres + ((size_t)img_local * QK_MAX + tid) * 3;
+    if (sums[tid][3]) {
+      const double n = (double)sums[tid][3];
+      o[0] = (double)sums[tid][0] / n; o[1] = (double)sums[tid][1] / n; o[2] = (double)sums[tid][2] / n;
+    } else {
+      o[0] = cen[tid][0]; o[1] = cen[tid][1]; o[2] = cen[tid][2];
+    }
+  }
+}
+
+// injected centres (fields.f0: [batch][k][3] float64) -> the padded workspace layout
+__global__ void k_quant_take(ImageSet s, int k, const double* f0, double* centres) {
+  const int img_local = image_of(s, blockIdx.x);
+  for (int i = threadIdx.x; i < k * 3; i += blockDim.x)
+    centres[(size_t)img_local * QK_MAX * 3 + i] = f0[(size_t)img_local * k * 3 + i];
+}
+
+// palette[c] = LAB2BGR(centres[c].astype(uint8)); astype on an in-range positive float truncates
+__global__ void k_quant_palette(ImageSet s, int k, const double* centres, uint32_t* palette) {
+  const int img_local = image_of(s, blockIdx.x);
+  const int c = threadIdx.x;
+  if (c >= k) return;
+  const double* ce = centres + ((size_t)img_local * QK_MAX + c) * 3;
+  palette[(size_t)img_local * QK_MAX + c] =
+      lab_inverse((int)wrap_u8(ce[0]), (int)wrap_u8(ce[1]), (int)wrap_u8(ce[2]));
+}
+
+// ---------------------------------------------------------------- apply --
+__global__ void __launch_bounds__(256) k_quant_apply(ImageSet s, int k, const double* centres, const uint32_t* palette) {
+  __shared__ uint16_t s_gam[256], s_cb[3072];
+  __shared__ double cen[QK_MAX][3];
+  __shared__ uint32_t pal[QK_MAX];
+  const int img_local = image_of(s, blockIdx.z);
+  if (threadIdx.x < k * 3) (&cen[0][0])[threadIdx.x] = centres[(size_t)img_local * QK_MAX * 3 + threadIdx.x];
+  if (threadIdx.x < k) pal[threadIdx.x] = palette[(size_t)img_local * QK_MAX + threadIdx.x];
+  stage_tables(s_gam, s_cb);
+  const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
+  uint8_t* out = s.out + (uint64_t)img_local * s.elems;
+  const int npix = s.h * s.w;
+  for (int p = blockIdx.x * 256 + threadIdx.x; p < npix; p += gridDim.x * 256) {
+    const uint8_t* px = img + (size_t)p * 3;
+    const uint32_t lab = lab_forward(px[0], px[1], px[2], s_gam, s_cb);
+    const double x0 = (double)(lab & 255u), x1 = (double)((lab >> 8) & 255u), x2 = (double)((lab >> 16) & 255u);
+    int best = 0;
+    double bd = 0.0;
+    for (int c = 0; c < k; ++c) {
+      // ((x - c) ** 2).sum(-1): products and sums rounded separately, left to right (no FMA)
+      const double d0 = __dsub_rn(x0, cen[c][0]), d1 = __dsub_rn(x1, cen[c][1]), d2 = __dsub_rn(x2, cen[c][2]);
+      const double d = __dadd_rn(__dadd_rn(__dmul_rn(d0, d0), __dmul_rn(d1, d1)), __dmul_rn(d2, d2));
+      if (c == 0 || d < bd) { bd = d; best = c; }       // np.argmin: first minimum
+    }
+    const uint32_t q = pal[best];
+    uint8_t* o = out + (size_t)p * 3;
+    o[0] = (uint8_t)q; o[1] = (uint8_t)(q >> 8); o[2] = (uint8_t)(q >> 16);
+  }
+}
+
+// test hook: the two colour conversions alone (dir 0: BGR -> Lab, 1: Lab -> BGR), n pixels
+__global__ void k_lab_convert(const uint8_t* in, uint8_t* out, size_t n, int dir) {
+  for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (size_t)gridDim.x * blockDim.x) {
+    const uint8_t* px = in + p * 3;
+    const uint32_t v = dir == 0 ? lab_forward(px[0], px[1], px[2], kLabGamma, kLabCbrt) : lab_inverse(px[0], px[1], px[2]);
+    out[p * 3] = (uint8_t)v; out[p * 3 + 1] = (uint8_t)(v >> 8); out[p * 3 + 2] = (uint8_t)(v >> 16);
+  }
+}
+
+cudaError_t launch_lab_convert(const uint8_t* in, uint8_t* out, size_t n, int dir, cudaStream_t st) {
+  k_lab_convert<<<148 * 8, 256, 0, st>>>(in, out, n, dir);
+  count_launch();
+  return cudaGetLastError();
+}
+
+size_t quant_table_bytes(int n) { return (size_t)n * QK_MAX * (3 * sizeof(double) + sizeof(uint32_t)) + 256; }
+
+int run_quant(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, uint8_t* tables, const b2d_fields* fields,
+              uint64_t seed, uint64_t first_global, cudaStream_t st) {
+  const int k = (int)sp.level;
+  double* centres = reinterpret_cast<double*>(tables);
+  uint32_t* palette = reinterpret_cast<uint32_t*>(tables + (size_t)p.n * QK_MAX * 3 * sizeof(double));
+  if (fields && fields->f0) k_quant_take<<<s.count, 128, 0, st>>>(s, k, fields->f0, centres);
+  else k_quant_fit<<<s.count, 256, 0, st>>>(s, k, (uint32_t)seed, (uint32_t)(seed >> 32), first_global, centres);
+  count_launch();
+  k_quant_palette<<<s.count, QK_MAX, 0, st>>>(s, k, centres, palette);
+  count_launch();
+  const unsigned bx = (unsigned)std::min<size_t>(((size_t)p.h * p.w + 255) / 256, 148 * 4);
+  k_quant_apply<<<dim3(bx, 1, s.count), 256, 0, st>>>(s, k, centres, palette);
+  count_launch();
+  const cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? B2D_OK : fail_cuda(e, "quant launch");
+}
+
+}  // namespace b2d

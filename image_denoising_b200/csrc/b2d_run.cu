@@ -31,6 +31,8 @@ static int validate_spec(const b2d_spec& s, int h, int w) {
     return fail(B2D_ERR_INVALID, "bloom needs H >= 300 (randint(1, H//100-2), Automold.py:583)");
   if (s.noise == B2D_NOISE_QUANT && (s.level < 1 || s.level > 32))
     return fail(B2D_ERR_INVALID, "quant k must be in [1, 32]");
+  if ((s.noise == B2D_NOISE_GAUSSIAN || s.noise == B2D_NOISE_SPECKLE) && !(s.level >= 0.0 && s.level <= 100.0))
+    return fail(B2D_ERR_INVALID, "gaussian / speckle var must be in [0, 100] (packed generator range)");
   (void)w;
   return B2D_OK;
 }
@@ -79,7 +81,7 @@ extern "C" int b2d_plan_create(b2d_plan** out, int device, int n, int h, int w, 
       }
     }
     const int nz = g.spec.noise;
-    if (nz == B2D_NOISE_BROWNIAN || nz == B2D_NOISE_QUANT || nz == B2D_NOISE_BLOOM) p->need_aux = true;
+    if (nz == B2D_NOISE_BROWNIAN) p->need_aux = true;
     if (nz == B2D_NOISE_PERIODIC) {
       bool have = false;
       for (const PeriodicTable& t : p->periodic) have = have || t.level == g.spec.level;
@@ -106,6 +108,15 @@ extern "C" int b2d_plan_create(b2d_plan** out, int device, int n, int h, int w, 
   p->off_scan = off;   off = align_up(off + (p->need_aux ? sizeof(double) * (size_t)p->brown_chunks * n : 0), 256);
   p->off_stage = off;  off = align_up(off + (size_t)p->elems * n, 256);
   p->off_aux = off;    off = align_up(off + (p->need_aux ? (size_t)p->elems * n : 0), 256);
+  p->off_pix = off;
+  {
+    size_t pix = 0;
+    for (const SpecGroup& g : p->groups) {
+      if (g.spec.noise == B2D_NOISE_QUANT) pix = std::max(pix, quant_table_bytes(n));
+      if (g.spec.noise == B2D_NOISE_BLOOM) pix = std::max(pix, bloom_table_bytes(n, h));
+    }
+    off = align_up(off + pix, 256);
+  }
   p->off_denoise = off;
   off += denoise_workspace_bytes(*p);
   p->ws_bytes = off;

@@ -147,6 +147,11 @@ int b2d_host_unregister(void* ptr);
 int b2d_noise_field(b2d_plan* plan, float* d_f0, float* d_f1, uint64_t seed,
                     uint64_t first_global_image_index, void* cuda_stream);
 
+/* Test hook: the uint8 colour conversions of the `quant` branch alone, on n_pixels interleaved
+ * 3-byte pixels (device pointers): direction 0 = cv2.cvtColor(COLOR_BGR2LAB), 1 = COLOR_LAB2BGR
+ * (lib/roi_data_layer/minibatch.py:496,507). */
+int b2d_lab_convert(const uint8_t* d_in, uint8_t* d_out, size_t n_pixels, int direction, void* cuda_stream);
+
 /* Per-image result statistics gathered after the run (8(e): the only data
  * that ever crosses GPUs): checksum = sum of bytes * (1 + index mod 251)
  * mod 2^64 of d_out[i]; sse = sum (d_out - d_ref)^2 (for PSNR vs clean). */
