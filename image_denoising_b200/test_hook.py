@@ -1,0 +1,42 @@
+"""Drop-in for the per-image corruption block of `test_net` (lib/model/test.py:189-1831):
+
+    for i in range(num_images):
+        img = cv2.imread(imdb.image_path_at(i))        # test.py:191
+        ... 1600 lines of closures + dispatch ...       # test.py:193-1831
+        scores, boxes = im_detect(sess, net, im)        # test.py:1836
+
+becomes `im = corrupt_for_test(img, noise, i)`; `get_test_blob` mirrors `_get_image_blob` of
+test.py:49-83 (mean subtraction, TEST.SCALES / TEST.MAX_SIZE resize)."""
+import numpy as np
+
+from . import api
+from .blob import im_list_to_blob
+from .config import cfg
+
+
+def corrupt_for_test(img, noise, index=0, rng=None, **overrides):
+    """One image, test.py semantics: uint8 BGR in, uint8 out, `mix` lists of test.py:1613-1639."""
+    return api.corrupt(img, noise, seed=cfg.RNG_SEED, index=index, side="test", rng=rng, **overrides)
+
+
+def corrupt_batch_for_test(imgs, noise, first_index=0, **overrides):
+    """Batched fast path: (N,H,W,3) uint8 host array, one spec, global indices first_index + i."""
+    return api.corrupt_host(np.ascontiguousarray(imgs), noise, seed=cfg.RNG_SEED, first_index=first_index,
+                            **overrides)
+
+
+def get_test_blob(im):
+    """test.py:49-83: image pyramid blob + scale factors."""
+    import cv2
+    im_orig = im.astype(np.float32, copy=True)
+    im_orig -= cfg.PIXEL_MEANS
+    im_size_min, im_size_max = np.min(im_orig.shape[0:2]), np.max(im_orig.shape[0:2])
+    processed_ims, im_scale_factors = [], []
+    for target_size in cfg.TEST.SCALES:
+        im_scale = float(target_size) / float(im_size_min)
+        if np.round(im_scale * im_size_max) > cfg.TEST.MAX_SIZE:
+            im_scale = float(cfg.TEST.MAX_SIZE) / float(im_size_max)
+        processed_ims.append(cv2.resize(im_orig, None, None, fx=im_scale, fy=im_scale,
+                                        interpolation=cv2.INTER_LINEAR))
+        im_scale_factors.append(im_scale)
+    return im_list_to_blob(processed_ims), np.array(im_scale_factors)
