@@ -22,6 +22,9 @@ namespace b2d {
 // group), c1 = substream (0 = primary draw, >0 = retries / extra draws),
 // (c2, c3) = global image index; key = seed.
 // ---------------------------------------------------------------------------
+#ifndef B2D_PHILOX_ROUNDS
+#define B2D_PHILOX_ROUNDS 10   /* Philox4x32-10 (Salmon et al.); 7 is the smallest Crush-resistant count */
+#endif
 #define B2D_PHILOX_M0 0xD2511F53u
 #define B2D_PHILOX_M1 0xCD9E8D57u
 #define B2D_PHILOX_W0 0x9E3779B9u
@@ -42,7 +45,7 @@ __host__ __device__ __forceinline__ void philox_round(uint32_t& c0, uint32_t& c1
 __host__ __device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2,
                                                         uint32_t c3, uint32_t k0, uint32_t k1) {
 #pragma unroll
-  for (int i = 0; i < 10; ++i) {
+  for (int i = 0; i < B2D_PHILOX_ROUNDS; ++i) {
     philox_round(c0, c1, c2, c3, k0, k1);
     k0 += B2D_PHILOX_W0;
     k1 += B2D_PHILOX_W1;

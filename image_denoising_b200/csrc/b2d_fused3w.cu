@@ -19,6 +19,8 @@
 #include "b2d_kernels.cuh"
 #include "b2d_filter3w.cuh"
 
+#include <cstdlib>
+
 namespace b2d {
 
 constexpr int FT_THREADS = 256;
@@ -182,12 +184,22 @@ static cudaError_t launch_filter(int filter, const ImageSet& s, const NoiseArgs&
 }
 
 cudaError_t launch_fused3_any(int kind, int filter, const ImageSet& s, const NoiseArgs& na, cudaStream_t st);
+cudaError_t launch_march3(int kind, int filter, const ImageSet& s, const NoiseArgs& na, cudaStream_t st);
+bool march3_supported(const ImageSet& s);
 
 cudaError_t launch_fused3(int kind, int filter, const ImageSet& s, const NoiseArgs& na, cudaStream_t st) {
   if (s.count <= 0) return cudaSuccess;
   const bool fast = s.rowbytes % 8 == 0 && s.elems < (1ull << 31) &&
                     ((reinterpret_cast<uintptr_t>(s.in) | reinterpret_cast<uintptr_t>(s.out)) & 7u) == 0;
   if (!fast) return launch_fused3_any(kind, filter, s, na, st);
+  // Measured on B200 (scripts/bench_combos.py, 512 x 600 x 1000): without a generator the
+  // row-marching persistent kernel (b2d_march3.cu) is 1.4-1.5x faster for gaus_blur / mean
+  // (0.32 / 0.35 ms vs 0.48 / 0.50 ms: no apron rows, register prefetch); with a generator in the
+  // prologue the tiles win (0.69 vs 0.78 ms for sap_mean: longer phases, fewer barriers), as they
+  // do for the register-heavy median.  B2D_MARCH=0 / 1 forces one of the two (profiling).
+  static const char* march_env = getenv("B2D_MARCH");
+  const bool march = march_env ? march_env[0] == '1' : (kind == NK_NONE && filter != FK_MEDIAN3);
+  if (march && march3_supported(s)) return launch_march3(kind, filter, s, na, st);
   switch (kind) {
     case NK_NONE: return launch_filter<NK_NONE>(filter, s, na, st);
     case NK_GAUSSIAN: return launch_filter<NK_GAUSSIAN>(filter, s, na, st);

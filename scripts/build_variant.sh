@@ -5,7 +5,7 @@ cd "$(dirname "$0")/../image_denoising_b200/csrc"
 mkdir -p ../../variants/obj_$1
 for f in *.cu; do
   o=../../variants/obj_$1/${f%.cu}.o
-  if [ "$f" = "b2d_fused3w.cu" ] || [ ! -f build/${f%.cu}.o ] || [ -n "$3" ]; then
+  if [ "$f" = "b2d_fused3w.cu" ] || [ "$f" = "b2d_march3.cu" ] || [ ! -f build/${f%.cu}.o ] || [ -n "$3" ]; then
     nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompiler -fPIC $2 -c $f -o $o &
   else
     cp build/${f%.cu}.o $o
