@@ -30,4 +30,9 @@ cudaError_t launch_lab_convert(const uint8_t* in, uint8_t* out, size_t n, int di
 // noise (operator `kind`, float where the reference keeps float) -> BayesShrink wavelet -> ->u8
 int run_wavelet(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, int kind, int mode, const NoiseArgs& na,
                 uint8_t* ws, cudaStream_t st);
+// db1 / 3 levels / H, W % 8 == 0 / generator mode: register-resident two-pass path (b2d_haar.cu)
+struct WvGeom;
+bool haar_supported(const b2d_plan& p, const b2d_spec& sp, int mode);
+int run_haar(const b2d_plan& p, const ImageSet& s, int kind, const NoiseArgs& na, const WvGeom& g_full, uint8_t* wbase,
+             size_t avail, const float (&inv)[3][3], cudaStream_t st);
 }  // namespace b2d

@@ -66,13 +66,6 @@ void wavelet_geometry(WvGeom& g, int wavelet, int levels_req, int h, int w) {
   g.chan_floats = (off + 3) & ~(size_t)3;
 }
 
-// ordered-int encoding so atomicMin/atomicMax work on floats of either sign
-__device__ __forceinline__ int f2ord(float f) {
-  const int b = __float_as_int(f);
-  return b ^ ((b >> 31) & 0x7fffffff);
-}
-__device__ __forceinline__ float ord2f(int o) { return __int_as_float(o ^ ((o >> 31) & 0x7fffffff)); }
-
 // skimage.color.rgb2ycbcr matrix (BT.601 studio swing), applied to channels in array order
 __constant__ float kYCC[3][3] = {{65.481f, 128.553f, 24.966f}, {-37.797f, -74.203f, 112.0f}, {112.0f, -93.786f, -18.214f}};
 
@@ -242,37 +235,65 @@ __global__ void __launch_bounds__(256) k_select_hist(WvGeom g, const float* ws, 
     if ((&sh[0][0])[i]) atomicAdd(&gh[i], (&sh[0][0])[i]);
 }
 
-__global__ void k_select_step(WvStats* stats, unsigned int* hist, int pass, int nplanes) {
-  const int z = blockIdx.x * blockDim.x + threadIdx.x;
-  if (z >= nplanes) return;
+// one CTA per plane: block-wide prefix sum over the digit histogram(s), pick the bin holding each rank
+__global__ void __launch_bounds__(256) k_select_step(WvStats* stats, unsigned int* hist, int pass) {
+  constexpr int PER = WV_BINS / 256;
+  const int z = blockIdx.x, t = threadIdx.x, lane = t & 31, wid = t >> 5;
   WvStats& st = stats[z];
   unsigned int* h0 = hist + (size_t)z * 2 * WV_BINS;
-  const int bins = pass == 2 ? 512 : WV_BINS;
+  const int bins = pass == 2 ? 512 : WV_BINS;                  // digits of pass 2 are 9 bits wide: upper bins stay 0
   const int bits = pass == 2 ? 9 : 11;
-  if (pass == 0) {
-    unsigned long long n = 0;
-    for (int i = 0; i < bins; ++i) n += h0[i];
-    st.count = n;
-    st.rank[0] = n ? (n - 1) / 2 : 0;
-    st.rank[1] = n / 2;
-    st.prefix[0] = st.prefix[1] = 0u;
-  }
+  __shared__ unsigned long long s_warp[8], s_rank[2];
+  __shared__ unsigned int s_sel[2];
   for (int r = 0; r < 2; ++r) {
     const unsigned int* hh = (pass == 0) ? h0 : h0 + r * WV_BINS;
-    unsigned long long k = st.rank[r], acc = 0;
-    int sel = bins - 1;
-    for (int i = 0; i < bins; ++i) {
-      if (acc + hh[i] > k) { sel = i; break; }
-      acc += hh[i];
+    unsigned int loc[PER];
+    unsigned long long sum = 0;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) { loc[i] = hh[t * PER + i]; sum += loc[i]; }
+    unsigned long long inc = sum;
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned long long v = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += v;
     }
-    st.rank[r] = k - acc;
-    st.prefix[r] = (st.prefix[r] << bits) | (unsigned int)sel;
+    __syncthreads();                                           // s_warp / s_sel of the previous rank are consumed
+    if (lane == 31) s_warp[wid] = inc;
+    __syncthreads();
+    unsigned long long before = inc - sum, total = 0;
+    for (int w = 0; w < 8; ++w) {
+      if (w < wid) before += s_warp[w];
+      total += s_warp[w];
+    }
+    unsigned long long k;
+    if (pass == 0) k = r == 0 ? (total ? (total - 1) / 2 : 0) : total / 2;
+    else k = st.rank[r];
+    if (t == 0) { s_sel[r] = (unsigned int)(bins - 1); s_rank[r] = k - total; }   // no bin holds the rank (empty plane)
+    __syncthreads();
+    if (before <= k && k < before + sum) {                     // exactly one thread
+      unsigned long long acc = before;
+      int sel = 0;
+#pragma unroll
+      for (int i = 0; i < PER; ++i) {
+        if (acc + loc[i] > k) { sel = t * PER + i; break; }
+        acc += loc[i];
+      }
+      s_sel[r] = (unsigned int)sel;
+      s_rank[r] = k - acc;
+    }
+    if (pass == 0 && r == 0 && t == 0) st.count = total;
   }
-  for (int i = 0; i < 2 * WV_BINS; ++i) h0[i] = 0u;            // ready for the next pass
-  if (pass == 2) {
-    const float v0 = __uint_as_float(st.prefix[0]), v1 = __uint_as_float(st.prefix[1]);
-    const double med = st.count ? 0.5 * ((double)v0 + (double)v1) : 0.0;
-    st.sigma = (float)(med / 0.6744897501960817);
+  __syncthreads();
+  for (int i = t; i < 2 * WV_BINS; i += 256) h0[i] = 0u;       // ready for the next pass
+  if (t == 0) {
+    for (int r = 0; r < 2; ++r) {
+      st.rank[r] = s_rank[r];
+      st.prefix[r] = ((pass == 0 ? 0u : st.prefix[r]) << bits) | s_sel[r];
+    }
+    if (pass == 2) {
+      const float v0 = __uint_as_float(st.prefix[0]), v1 = __uint_as_float(st.prefix[1]);
+      const double med = st.count ? 0.5 * ((double)v0 + (double)v1) : 0.0;
+      st.sigma = (float)(med / 0.6744897501960817);
+    }
   }
 }
 
@@ -296,11 +317,7 @@ __global__ void k_thresholds(WvGeom g, WvStats* stats, int nplanes) {
 }
 
 // ------------------------------------------------------------ 4. inverse DWT
-__device__ __forceinline__ float soft(float d, float thr) {
-  // pywt.threshold(d, thr, 'soft') = d * max(1 - thr / |d|, 0)
-  const float m = fabsf(d);
-  return m > 0.0f ? d * fmaxf(1.0f - thr / m, 0.0f) : 0.0f;
-}
+__device__ __forceinline__ float soft(float d, float thr) { return wv_soft(d, thr); }
 
 // one axis of pywt's idwt: out[k] = sum_i a[i] rec_lo[k + F - 2 - 2 i] + d[i] rec_hi[k + F - 2 - 2 i]
 template <class LoadA, class LoadD>
@@ -428,6 +445,24 @@ size_t wavelet_workspace_bytes(const b2d_plan& p) {
   return need;
 }
 
+void wavelet_stats_begin(WvStats* stats, unsigned int* hist, int planes, cudaStream_t st) {
+  k_wv_init<<<(planes + 127) / 128, 128, 0, st>>>(stats, planes);
+  cudaMemsetAsync(hist, 0, (size_t)planes * 2 * WV_BINS * sizeof(unsigned int), st);
+  count_launch();
+}
+
+void wavelet_sigma_thresholds(const WvGeom& g, const float* ws, WvStats* stats, unsigned int* hist, int planes,
+                              cudaStream_t st) {
+  auto blocks = [](size_t n) { return (unsigned)std::min<size_t>((n + 255) / 256, 148 * 8); };
+  for (int pass = 0; pass < 3; ++pass) {
+    k_select_hist<<<dim3(std::min(blocks((size_t)g.h[1] * g.w[1]), 32u), 1, planes), 256, 0, st>>>(g, ws, stats, hist, pass);
+    k_select_step<<<planes, 256, 0, st>>>(stats, hist, pass);
+    count_launch(); count_launch();
+  }
+  k_thresholds<<<(planes + 63) / 64, 64, 0, st>>>(g, stats, planes);
+  count_launch();
+}
+
 template <int KIND>
 static void launch_color(int mode, dim3 grid, cudaStream_t st, const ImageSet& s, const NoiseArgs& na, const WvGeom& g,
                          float* ws, WvStats* stats, int first) {
@@ -461,12 +496,12 @@ int run_wavelet(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, int ki
   for (int i = 0; i < 3; ++i)
     for (int j = 0; j < 3; ++j) fa.inv[i][j] = (float)inv[i][j];
   auto blocks = [](size_t n) { return (unsigned)std::min<size_t>((n + 255) / 256, 148 * 8); };
+  if (haar_supported(p, sp, mode)) return run_haar(p, s, kind, na, g, wbase, wavelet_workspace_bytes(p), fa.inv, st);
 
   for (int first = 0; first < s.count; first += chunk) {
     const int cnt = std::min(chunk, s.count - first);
     const int planes = cnt * 3;
-    k_wv_init<<<(planes + 127) / 128, 128, 0, st>>>(stats, planes);
-    cudaMemsetAsync(hist, 0, (size_t)planes * 2 * WV_BINS * sizeof(unsigned int), st);
+    wavelet_stats_begin(stats, hist, planes, st);
     const dim3 cgrid(blocks(((size_t)p.h * p.w + 7) / 8), 1, cnt);
     switch (kind) {
       case NK_NONE: launch_color<NK_NONE>(mode, cgrid, st, s, na, g, ws, stats, first); break;
@@ -489,13 +524,7 @@ int run_wavelet(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, int ki
       k_band_energy<<<dim3(std::min(blocks((size_t)g.h[l] * g.w[l]), 64u), 1, planes), 256, 0, st>>>(g, ws, stats, l);
       count_launch(); count_launch(); count_launch();
     }
-    for (int pass = 0; pass < 3; ++pass) {
-      k_select_hist<<<dim3(std::min(blocks((size_t)g.h[1] * g.w[1]), 32u), 1, planes), 256, 0, st>>>(g, ws, stats, hist, pass);
-      k_select_step<<<(planes + 63) / 64, 64, 0, st>>>(stats, hist, pass, planes);
-      count_launch(); count_launch();
-    }
-    k_thresholds<<<(planes + 63) / 64, 64, 0, st>>>(g, stats, planes);
-    count_launch();
+    wavelet_sigma_thresholds(g, ws, stats, hist, planes, st);
     for (int l = g.L; l >= 1; --l) {
       k_idwt_rows<<<dim3(blocks((size_t)g.h[l] * g.w[l - 1]), 1, planes), 256, 0, st>>>(g, ws, stats, l);
       k_idwt_cols<<<dim3(blocks((size_t)g.h[l - 1] * g.w[l - 1]), 1, planes), 256, 0, st>>>(g, ws, l);

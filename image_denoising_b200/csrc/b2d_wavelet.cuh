@@ -31,4 +31,23 @@ struct WvStats {                 // one per (image in chunk, channel)
 
 void wavelet_geometry(WvGeom& g, int wavelet, int levels_req, int h, int w);
 
+#ifdef __CUDACC__
+// order-preserving float <-> int map for atomicMin / atomicMax
+__device__ __forceinline__ int f2ord(float f) {
+  const int i = __float_as_int(f);
+  return i ^ ((i >> 31) & 0x7fffffff);
+}
+__device__ __forceinline__ float ord2f(int o) { return __int_as_float(o ^ ((o >> 31) & 0x7fffffff)); }
+
+// pywt.threshold(d, thr, 'soft') = d * max(1 - thr / |d|, 0) = sign(d) * max(|d| - thr, 0): the
+// second form needs no division (3 instructions) and differs from the first by rounding only
+__device__ __forceinline__ float wv_soft(float d, float thr) { return copysignf(fmaxf(fabsf(d) - thr, 0.0f), d); }
+
+// shared between the general path (b2d_wavelet.cu) and the Haar fast path (b2d_haar.cu)
+void wavelet_stats_begin(WvStats* stats, unsigned int* hist, int planes, cudaStream_t st);
+// median(|dd_1| != 0) -> sigma, then the BayesShrink thresholds; dd_1 of plane z at ws + z * g.chan_floats + g.off_det[1][2]
+void wavelet_sigma_thresholds(const WvGeom& g, const float* ws, WvStats* stats, unsigned int* hist, int planes,
+                              cudaStream_t st);
+#endif
+
 }  // namespace b2d

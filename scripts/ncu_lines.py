@@ -1,6 +1,8 @@
 #!/usr/bin/env python
 """Aggregate an `ncu --page source --csv --print-source cuda,sass` dump per CUDA source line.
-usage: ncu -i rep.ncu-rep --page source --csv --print-source cuda,sass > x.csv; python scripts/ncu_lines.py x.csv [top]"""
+usage: ncu -i rep.ncu-rep --page source --csv --print-source cuda,sass > x.csv; python scripts/ncu_lines.py x.csv [top]
+The dump is a sequence of sections (one per kernel x source file): `File Path`, `Function Name`,
+a `Line No` header, then one summary row per source line followed by its SASS rows."""
 import csv
 import sys
 from collections import defaultdict
@@ -8,23 +10,19 @@ from collections import defaultdict
 rows = list(csv.reader(open(sys.argv[1])))
 top = int(sys.argv[2]) if len(sys.argv) > 2 else 25
 kernel, fname, hdr = None, None, None
-agg = defaultdict(lambda: defaultdict(lambda: [0, 0, ""]))   # kernel -> (file,line) -> [inst, samples, text]
-cur = None
+agg = defaultdict(dict)                      # kernel -> (file, line) -> [inst, samples, text]
 for r in rows:
     if not r:
         continue
-    if r[0] == "Kernel Name":
+    if r[0] in ("Kernel Name", "Function Name"):
         kernel = r[1]; continue
-    if r[0] == "File Name":
+    if r[0] in ("File Name", "File Path"):
         fname = r[1].split("/")[-1]; continue
     if r[0] == "Line No":
         hdr = r; ii = hdr.index("Instructions Executed"); si = hdr.index("# Samples"); continue
-    if hdr is None:
+    if hdr is None or r[0] == "" or len(r) <= ii or not r[ii].isdigit():
         continue
-    if r[0] != "":
-        cur = (fname, r[0]); agg[kernel][cur][2] = r[1].strip()[:90]; continue
-    if cur and len(r) > ii and r[ii].isdigit():
-        agg[kernel][cur][0] += int(r[ii]); agg[kernel][cur][1] += int(r[si]) if r[si].isdigit() else 0
+    agg[kernel][(fname, r[0])] = [int(r[ii]), int(r[si]) if r[si].isdigit() else 0, r[1].strip()[:90]]
 for k, d in agg.items():
     tot = sum(v[0] for v in d.values()); ts = sum(v[1] for v in d.values()) or 1
     if not tot:

@@ -72,3 +72,40 @@ def test_generator_mode_denoises(cuda):
     mse_n = ((noisy - x.float()) ** 2).mean().item()
     mse_d = ((den - x.float()) ** 2).mean().item()
     assert mse_d < 0.6 * mse_n, (mse_n, mse_d)
+
+
+_HAAR_SPECS = ["gaussian_wavelet_var1.5", "speckle_wavelet_var1.0", "sap_wavelet_var0.4", "uniform_wavelet_var0.6",
+               "gamma_wavelet_var0.1", "rayleigh_wavelet_var0.2", "poisson_wavelet", "periodic_wavelet_var100",
+               "shader_wavelet", "original_wavelet"]
+_HAAR_SCRIPT = r"""
+import sys, numpy as np, torch
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[1] + "/tests")
+from conftest import synth_batch
+from image_denoising_b200 import api
+out = {}
+for h, w in ((64, 96), (200, 1000)):
+    batch = torch.from_numpy(synth_batch(3, h, w, seed=23, kind="smooth")).cuda()
+    for spec in sys.argv[3:]:
+        out["%s@%dx%d" % (spec, h, w)] = api.apply(batch, spec, seed=11, first_index=5, wavelet="db1", levels=3).cpu().numpy()
+np.savez(sys.argv[2], **out)
+"""
+
+
+def test_haar_fast_path_equals_general_path(cuda, tmp_path):
+    """Generator mode, every noise operator: the register-resident db1 / 3-level path (b2d_haar.cu)
+    against the general multi-pass path (B2D_HAAR=0) of the same library, same Philox counters.
+    Both compute fp32 with the same operation order; only the band energies are summed differently."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = {}
+    for tag, env in (("fast", {}), ("general", {"B2D_HAAR": "0"})):
+        path = str(tmp_path / (tag + ".npz"))
+        subprocess.run([sys.executable, "-c", _HAAR_SCRIPT, root, path] + _HAAR_SPECS, check=True,
+                       env=dict(os.environ, **env), timeout=600)
+        outs[tag] = dict(np.load(path))
+    assert set(outs["fast"]) == set(outs["general"]) and len(outs["fast"]) == 2 * len(_HAAR_SPECS), sorted(outs["fast"])
+    for key, a in outs["fast"].items():
+        d = np.abs(a.astype(int) - outs["general"][key].astype(int))
+        assert d.max() <= 1 and (d > 0).mean() < 2e-3, (key, d.max(), (d > 0).mean())
