@@ -221,13 +221,33 @@ __global__ void __launch_bounds__(256) k_select_hist(WvGeom g, const float* ws, 
   const unsigned int mask = pass == 2 ? 0x1ffu : 0x7ffu;
   const unsigned int p0 = stats[blockIdx.z].prefix[0], p1 = stats[blockIdx.z].prefix[1];
   const int hshift = pass == 0 ? 31 : pass == 1 ? 20 : 9;     // bits above the current digit
-  for (int t = blockIdx.x * 256 + threadIdx.x; t < n; t += gridDim.x * 256) {
-    const unsigned int b = __float_as_uint(dd[t]) & 0x7fffffffu;
-    if (b == 0u) continue;
+  auto tally = [&](float v) {
+    const unsigned int b = __float_as_uint(v) & 0x7fffffffu;
+    if (b == 0u) return;
     const unsigned int digit = (b >> shift) & mask;
     const unsigned int high = pass == 0 ? 0u : (b >> hshift);
     if (pass == 0 || high == p0) atomicAdd(&sh[0][digit], 1u);
     if (pass != 0 && high == p1) atomicAdd(&sh[1][digit], 1u);
+  };
+  // 16-byte loads, two in flight per thread: the pass is a pure stream of the band
+  const int head = min(n, (int)((16u - ((unsigned)reinterpret_cast<uintptr_t>(dd) & 15u)) & 15u) / 4);
+  const int nvec = (n - head) / 4;
+  const float4* dv = reinterpret_cast<const float4*>(dd + head);
+  const int stride = gridDim.x * 256;
+  int t = blockIdx.x * 256 + threadIdx.x;
+  for (; t + stride < nvec; t += 2 * stride) {
+    const float4 a = __ldg(dv + t), b = __ldg(dv + t + stride);
+    tally(a.x); tally(a.y); tally(a.z); tally(a.w);
+    tally(b.x); tally(b.y); tally(b.z); tally(b.w);
+  }
+  if (t < nvec) {
+    const float4 a = __ldg(dv + t);
+    tally(a.x); tally(a.y); tally(a.z); tally(a.w);
+  }
+  if (blockIdx.x == 0) {
+    if ((int)threadIdx.x < head) tally(dd[threadIdx.x]);
+    const int tail = head + nvec * 4 + threadIdx.x;
+    if (tail < n) tally(dd[tail]);
   }
   __syncthreads();
   unsigned int* gh = hist + (size_t)blockIdx.z * 2 * WV_BINS;

@@ -65,6 +65,16 @@ KERNEL(mix_prmt_imad, , if (j & 1) asm volatile("prmt.b32 %0, %0, %1, 0x4321;" :
 KERNEL(mix_lop_ffma, | 0x3f800000u, if (j & 1) asm volatile("lop3.b32 %0, %0, %1, %2, 0xEA;" : "+r"(a[j]) : "r"(0x007fffffu), "r"(0x3f800000u)); else { float f = __uint_as_float(a[j]); f = fmaf(f, 0.999f, 1e-3f); a[j] = __float_as_uint(f); })
 KERNEL(mix_mufu_alu, | 0x3f800000u, if ((j & 7) == 0) { float f = __uint_as_float(a[j]); asm volatile("lg2.approx.ftz.f32 %0, %0;" : "+f"(f)); a[j] = __float_as_uint(f); } else asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[j]) : "r"(b), "r"(c)))
 
+// packed fp32 pairs (sm_100 f32x2): one instruction, two lanes of a 64-bit register pair
+#define PK(lo, hi) ({ unsigned long long _v; asm("mov.b64 %0, {%1,%2};" : "=l"(_v) : "r"(lo), "r"(hi)); _v; })
+#define UPK(v, lo, hi) asm("mov.b64 {%0,%1}, %2;" : "=r"(lo), "=r"(hi) : "l"(v))
+KERNEL(ffma2, | 0x3f800000u, if (!(j & 1)) { unsigned long long v = PK(a[j], a[j + 1]); const unsigned long long m = PK(0x3f7fbe77u, 0x3f7fbe77u), k = PK(0x3a83126fu, 0x3a83126fu); asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(v) : "l"(m), "l"(k)); UPK(v, a[j], a[j + 1]); })
+KERNEL(fadd2, | 0x3f800000u, if (!(j & 1)) { unsigned long long v = PK(a[j], a[j + 1]); const unsigned long long k = PK(0x3a83126fu, 0x3a83126fu); asm volatile("add.rn.f32x2 %0, %0, %1;" : "+l"(v) : "l"(k)); UPK(v, a[j], a[j + 1]); })
+KERNEL(fmul2, | 0x3f800000u, if (!(j & 1)) { unsigned long long v = PK(a[j], a[j + 1]); const unsigned long long m = PK(0x3f7fbe77u, 0x3f7fbe77u); asm volatile("mul.rn.f32x2 %0, %0, %1;" : "+l"(v) : "l"(m)); UPK(v, a[j], a[j + 1]); })
+KERNEL(fmnmx, | 0x3f800000u, { float f = __uint_as_float(a[j]); f = fminf(f, __uint_as_float(b | 0x3f000000u)); a[j] = __float_as_uint(f) + 1u; })
+KERNEL(fsel, | 0x3f800000u, { a[j] = (b & (1u << j)) ? a[j] + 1u : c; })
+KERNEL(shfl, , a[j] = __shfl_xor_sync(0xffffffffu, a[j], 1))
+
 // shared-memory read throughput
 template <int VEC>
 __global__ void __launch_bounds__(256) k_lds(uint32_t* out, uint32_t s, long long* cyc) {
@@ -108,6 +118,7 @@ int main() {
       E(mufu_lg2, full), E(mufu_lg2_only, full), E(mufu_sin, full), E(mufu_sqrt, full), E(mufu_rsqrt, full),
       E(mufu_ex2, full), E(mufu_rcp, full), E(i2f, full), E(i2f_u16, full), E(f2i, full), E(f2i_only, full),
       E(philox_round, full / 2), E(mix_prmt_imad, full), E(mix_lop_ffma, full), E(mix_mufu_alu, full),
+      E(ffma2, full / 2), E(fadd2, full / 2), E(fmul2, full / 2), E(fmnmx, full), E(fsel, full), E(shfl, full),
       {"lds32", k_lds<1>, 16.0}, {"lds64", k_lds<2>, 16.0}, {"lds128", k_lds<4>, 16.0},
   };
   printf("device %s, %d SMs, %d MHz max\n", p.name, nsm, p.clockRate / 1000);
