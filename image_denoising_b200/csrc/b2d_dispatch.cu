@@ -95,7 +95,21 @@ int run_group(const RunCtx& c, const SpecGroup& g, int lo, int hi) {
       float* par = reinterpret_cast<float*>(c.ws + p->off_par);
       CK(launch_poisson_vals(s, reinterpret_cast<uint32_t*>(c.ws + p->off_bitmap), par, p->n, c.st));
       na.img_par = par;
-      break;
+      if (inject) break;                               // injected counts: the per-element operator divides and clips
+      // generator mode: alias-table sampler writes the corrupted uint8 image, the denoiser reads it
+      uint8_t* dst = sp.denoise == B2D_DENOISE_NONE ? c.out : stage;
+      ImageSet ps = s;
+      ps.out = dst;
+      CK(launch_poisson(ps, na, p->d_poisson, c.st));
+      if (sp.denoise == B2D_DENOISE_NONE) return B2D_OK;
+      ImageSet ds = s;
+      ds.in = stage;
+      if (sp.denoise == B2D_DENOISE_WAVELET) {
+        NoiseArgs none{};
+        none.elems = p->elems;
+        return run_wavelet(*p, sp, ds, NK_NONE, NM_GEN, none, c.ws, c.st);
+      }
+      return denoise_u8(c, sp, ds);
     }
     case B2D_NOISE_PERIODIC: {
       kind = NK_TABLE_ADD;

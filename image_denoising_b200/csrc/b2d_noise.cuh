@@ -504,6 +504,49 @@ struct PackedNormal {
     return make_uint2(prmt(l01, l23, 0x6420u), prmt(l45, l67, 0x6420u));
   }
 };
+// shader: min(255, 3 v) of the RGB-ordered decode = swap bytes 0 and 2 of every pixel, then a
+// saturating x3 on u16x2 lanes.  Output byte i of the group (channel c = (8 g + i) % 3) reads byte
+// i + 2 - 2 c: the sources span [-2, +9] around the group, so the two neighbouring words are
+// fetched (L1 hits) and three PRMTs with phase-dependent selectors do the swap.
+template <>
+struct PackedNoise<NK_SHADER> {
+  static constexpr bool kNative = true;
+  static __device__ __forceinline__ uint32_t times3_sat(uint32_t w) {
+    const uint32_t e = __vminu2((w & 0x00ff00ffu) * 3u, 0x00ff00ffu);
+    const uint32_t o = __vminu2(((w >> 8) & 0x00ff00ffu) * 3u, 0x00ff00ffu);
+    return prmt(e, o, 0x6240u);
+  }
+  static __device__ __forceinline__ uint32_t word_at(const GroupCtx& g, const NoiseArgs& a, int64_t e) {
+    if (e < 0) return 0u;
+    const uint8_t* p = g.img + e;
+    if ((uint64_t)e + 4u <= a.elems && (reinterpret_cast<uintptr_t>(p) & 3u) == 0)
+      return __ldg(reinterpret_cast<const uint32_t*>(p));
+    uint32_t w = 0u;
+    for (int i = 0; i < 4; ++i)
+      if ((uint64_t)e + i < a.elems) w |= (uint32_t)__ldg(p + i) << (8 * i);
+    return w;
+  }
+  static __device__ __forceinline__ uint2 apply(const NoiseArgs& a, const GroupCtx& g, uint2 w) {
+    if (a.u0 != 0u) return make_uint2(times3_sat(w.x), times3_sat(w.y));      // compat: keep BGR order
+    const int64_t e0 = (int64_t)g.group * 8;
+    const uint32_t prev = word_at(g, a, e0 - 4), next = word_at(g, a, e0 + 8);
+    // per output byte: channel c -> source L (byte i - 2, c = 2), M (byte i, c = 1) or R (byte i + 2, c = 0)
+    const uint32_t lx = prmt(prev, w.x, 0x5432u), rx = prmt(w.x, w.y, 0x5432u);
+    const uint32_t ly = rx, ry = prmt(w.y, next, 0x5432u);
+    // selector nibbles over {A = (L, M): 0-3 L, 4-7 M} then {(A', R): 0-3 A', 4-7 R}
+    const uint32_t ph = (uint32_t)((g.group * 8u) % 3u);                      // channel of byte 0
+    // channel pattern of bytes 0..3 for ph = 0, 1, 2: (0,1,2,0) (1,2,0,1) (2,0,1,2); bytes 4..7 start at ph + 1
+    auto swap4 = [](uint32_t l, uint32_t m, uint32_t r, uint32_t phase) {
+      // first PRMT: c = 2 -> L byte i, else M byte i;  second: c = 0 -> R byte i, else keep
+      const uint32_t selA = phase == 0 ? 0x7254u : phase == 1 ? 0x7614u : 0x3650u;
+      const uint32_t selB = phase == 0 ? 0x7214u : phase == 1 ? 0x3610u : 0x3250u;
+      return prmt(prmt(l, m, selA), r, selB);
+    };
+    const uint32_t ox = swap4(lx, w.x, rx, ph), oy = swap4(ly, w.y, ry, (ph + 1u) % 3u);
+    return make_uint2(times3_sat(ox), times3_sat(oy));
+  }
+};
+
 template <> struct PackedNoise<NK_GAUSSIAN> : PackedNormal<false> {};
 template <> struct PackedNoise<NK_SPECKLE> : PackedNormal<true> {};
 

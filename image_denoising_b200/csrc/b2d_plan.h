@@ -29,6 +29,7 @@ struct b2d_plan {
   uint64_t elems;
   std::vector<b2d::SpecGroup> groups;
   std::vector<b2d::PeriodicTable> periodic;
+  uint8_t* d_poisson;        // alias tables of the Poisson generator (b2d_poisson.cu), when a group needs them
   // workspace layout (byte offsets into the caller's d_ws)
   size_t ws_bytes, off_par, off_bitmap, off_stage, off_aux, off_scan, off_denoise, off_pix;
   uint32_t brown_chunks;

@@ -12,6 +12,9 @@ struct BrownianArgs {
 };
 
 uint32_t brownian_chunks(uint64_t elems);
+// generator-mode Poisson through per-`vals` alias tables (b2d_poisson.cu); img_par = vals per image
+cudaError_t upload_poisson_tables(uint8_t** d_tables);
+cudaError_t launch_poisson(const ImageSet& s, const NoiseArgs& na, const uint8_t* tables, cudaStream_t st);
 cudaError_t launch_poisson_vals(const ImageSet& s, uint32_t* bitmaps, float* vals, int n_batch, cudaStream_t st);
 cudaError_t launch_periodic_table(uint8_t* tab, uint64_t n, double lim, cudaStream_t st);
 cudaError_t launch_brownian_field(const ImageSet& s, const NoiseArgs& na, const BrownianArgs& ba, bool inject,

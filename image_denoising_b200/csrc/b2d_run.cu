@@ -57,6 +57,7 @@ extern "C" int b2d_plan_create(b2d_plan** out, int device, int n, int h, int w, 
   p->device = device; p->n = n; p->h = h; p->w = w; p->rowbytes = 3 * w;
   p->elems = (uint64_t)h * w * 3;
   p->h_d_in = p->h_d_out = p->h_d_ws = nullptr;
+  p->d_poisson = nullptr;
   p->h_ready = false;
   p->need_aux = false;
   // group images by identical spec, keeping first-appearance order
@@ -82,6 +83,13 @@ extern "C" int b2d_plan_create(b2d_plan** out, int device, int n, int h, int w, 
     }
     const int nz = g.spec.noise;
     if (nz == B2D_NOISE_BROWNIAN) p->need_aux = true;
+    if (nz == B2D_NOISE_POISSON && !p->d_poisson) {
+      const cudaError_t e = upload_poisson_tables(&p->d_poisson);
+      if (e != cudaSuccess) {
+        b2d_plan_destroy(p);
+        return fail_cuda(e, "poisson tables");
+      }
+    }
     if (nz == B2D_NOISE_PERIODIC) {
       bool have = false;
       for (const PeriodicTable& t : p->periodic) have = have || t.level == g.spec.level;
@@ -137,6 +145,7 @@ extern "C" void b2d_plan_destroy(b2d_plan* p) {
     if (g.d_list) cudaFree(g.d_list);
   for (PeriodicTable& t : p->periodic)
     if (t.d_tab) cudaFree(t.d_tab);
+  if (p->d_poisson) cudaFree(p->d_poisson);
   if (p->h_d_in) cudaFree(p->h_d_in);
   if (p->h_d_out) cudaFree(p->h_d_out);
   if (p->h_d_ws) cudaFree(p->h_d_ws);

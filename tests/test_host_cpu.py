@@ -4,6 +4,7 @@ import os
 import random
 import re
 
+import numpy as np
 import pytest
 
 from image_denoising_b200 import _lib, spec
@@ -102,3 +103,36 @@ def test_plan_create_fails_loudly_without_gpu():
     from image_denoising_b200 import api
     with pytest.raises(RuntimeError):
         api.Plan(1, 8, 8, "sap_mean_var0.4")
+
+
+@pytest.mark.parametrize("log2_vals", [8, 5, 0])
+def test_poisson_alias_table_represents_the_pmf(log2_vals):
+    """b2d_poisson_table (host code of the library, no GPU): the alias table of input value v must
+    reproduce the pmf of (255 * clip(Poisson(v / 255 * vals) / vals, 0, 1)).astype(uint8)
+    (skimage random_noise 'poisson' + the reference's ->u8, minibatch.py:211-213) to 2^-16 per
+    outcome plus the mass folded away by the rounding."""
+    import ctypes
+    from scipy.stats import poisson
+    L = _lib.lib()
+    tab = np.zeros(65536, np.uint16)
+    _lib.check(L.b2d_poisson_table(log2_vals, tab.ctypes.data_as(ctypes.c_void_p)))
+    tab = tab.reshape(256, 256)
+    thr, alias = (tab & 0xff).astype(np.int64), (tab >> 8).astype(np.int64)
+    vals = 1 << log2_vals
+    k = np.arange(vals + 1)
+    out_of_k = (255 * np.minimum(k, vals)) >> log2_vals
+    for v in (0, 1, 7, 64, 128, 200, 255):
+        lam = v / 255.0 * vals
+        pk = poisson.pmf(k[:-1], lam) if lam > 0 else np.eye(1, vals, 0)[0]
+        want = np.bincount(out_of_k[:-1], weights=pk, minlength=256)
+        want[255] += max(0.0, 1.0 - pk.sum())
+        # mass of outcome b = sum over slots of [own share] + [alias share], in units of 2^-16
+        own = np.where(alias[v] == np.arange(256), 256, thr[v])
+        got = np.bincount(np.arange(256), weights=own, minlength=256) + \
+            np.bincount(alias[v], weights=256 - own, minlength=256)
+        assert got.sum() == 65536
+        assert np.abs(got / 65536.0 - want).max() <= 1.0 / 65536 + 1e-12, (log2_vals, v)
+        mean_err = abs((got / 65536.0 * np.arange(256)).sum() - (want * np.arange(256)).sum())
+        assert mean_err < 2e-3, (log2_vals, v, mean_err)
+    with pytest.raises(_lib.B2DError):
+        _lib.check(L.b2d_poisson_table(9, tab.ctypes.data_as(ctypes.c_void_p)))
