@@ -77,7 +77,7 @@ static void build_row(int t, int v, uint16_t* row) {
   for (int i = 0; i < PO_SLOTS; ++i) {
     // u (8 random bits) < thr keeps the slot; thr == 256 (always) is stored as alias = slot
     const int th = thr[i] >= 256 ? 255 : thr[i], al = thr[i] >= 256 ? i : alias[i];
-    row[i] = (uint16_t)(th | (al << 8));
+    row[i] = (uint16_t)(al | (th << 8));
   }
 }
 
@@ -126,16 +126,20 @@ __global__ void __launch_bounds__(PO_THREADS, 1) k_poisson(ImageSet s, NoiseArgs
     GroupCtx gc{(uint32_t)img_local, grp, img};
     const uint4 ra = group_random(na, gc, 0);
     const uint32_t rw[4] = {ra.x, ra.y, ra.z, ra.w};
+    // 16 random bits per element: low byte = slot, high byte = u.  One PRMT builds the table indices
+    // (v << 8 | slot) of two elements; `r16 < (entry & 0xff00)` is u < threshold because slot < 256.
     uint32_t o[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const uint32_t v = ((i < 4 ? w.x : w.y) >> (8 * (i & 3))) & 0xffu;
-      const uint32_t r16 = (rw[i >> 1] >> (16 * (i & 1))) & 0xffffu;
-      const uint32_t slot = r16 & 0xffu, u = r16 >> 8;
-      const uint32_t e = tab[(v << 8) | slot];
-      o[i] = u < (e & 0xffu) ? slot : (e >> 8);
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t wj = j < 2 ? w.x : w.y;
+      const uint32_t idx2 = __byte_perm(wj, rw[j], (j & 1) ? 0x3624u : 0x1604u);   // [slot0, v0, slot1, v1]
+      const uint32_t r0 = rw[j] & 0xffffu, r1 = rw[j] >> 16;
+      const uint32_t e0v = tab[idx2 & 0xffffu], e1v = tab[idx2 >> 16];
+      o[2 * j] = r0 < (e0v & 0xff00u) ? r0 : e0v;                                // low byte = result
+      o[2 * j + 1] = r1 < (e1v & 0xff00u) ? r1 : e1v;
     }
-    const uint2 r = make_uint2(pack4(o[0], o[1], o[2], o[3]), pack4(o[4], o[5], o[6], o[7]));
+    const uint2 r = make_uint2(__byte_perm(__byte_perm(o[0], o[1], 0x0040), __byte_perm(o[2], o[3], 0x0040), 0x5410),
+                               __byte_perm(__byte_perm(o[4], o[5], 0x0040), __byte_perm(o[6], o[7], 0x0040), 0x5410));
     if (full) {
       *reinterpret_cast<uint2*>(out + e0) = r;
     } else {
@@ -162,6 +166,17 @@ cudaError_t launch_poisson(const ImageSet& s, const NoiseArgs& na, const uint8_t
   // one CTA per SM is resident (192 KB of shared memory): about two waves over the batch, and no
   // segment shorter than 16 passes of the CTA so the table load stays a small share
   int segs = std::max(1, (2 * sms + s.count - 1) / s.count);
+  {                                                                   // fewest segments within 3 % of the best wave fill
+    double best = 0.0;
+    for (int c = segs; c < segs + 8; ++c) {
+      const long total = (long)c * s.count;
+      best = std::max(best, (double)total / (double)(((total + sms - 1) / sms) * sms));
+    }
+    for (int c = segs; c < segs + 8; ++c) {
+      const long total = (long)c * s.count;
+      if ((double)total / (double)(((total + sms - 1) / sms) * sms) >= best - 0.03) { segs = c; break; }
+    }
+  }
   segs = (int)std::min<uint32_t>((uint32_t)segs, std::max<uint32_t>(1u, ngroups / (16u * PO_THREADS)));
   const int seg_groups = (int)((ngroups + segs - 1) / segs);
   k_poisson<<<dim3((unsigned)segs, (unsigned)s.count, 1), PO_THREADS, PO_TABLE_BYTES, st>>>(s, na, tables, seg_groups);

@@ -9,19 +9,48 @@
 namespace b2d {
 
 // ---------------------------------------------------------------- poisson --
+// 256-bit presence bitmap of the byte values of one image.  A CTA starts from what the other CTAs
+// of the image have already published and stops as soon as the bitmap is full (every value seen):
+// natural images saturate after a few KB, so the pass usually costs far less than one read of the
+// batch; the worst case (few distinct values) streams the image once with 16-byte loads.
 __global__ void __launch_bounds__(256) k_unique_bitmap(ImageSet s, uint32_t* bitmaps /* [n][8] */) {
-  __shared__ uint32_t bm[8];
-  if (threadIdx.x < 8) bm[threadIdx.x] = 0u;
-  __syncthreads();
+  __shared__ __align__(16) uint32_t bm[8];
   const int img_local = image_of(s, blockIdx.z);
   const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
-  for (uint64_t e = (uint64_t)blockIdx.x * 256 + threadIdx.x; e < s.elems; e += (uint64_t)gridDim.x * 256) {
-    const uint32_t b = __ldg(img + e);
+  uint32_t* gbm = bitmaps + (size_t)img_local * 8;
+  uint32_t seen = 0u;
+  if (threadIdx.x < 8) bm[threadIdx.x] = seen = *reinterpret_cast<volatile uint32_t*>(gbm + threadIdx.x);
+  __syncthreads();
+  auto full = [&]() {
+    const volatile uint32_t* v = bm;
+    return (v[0] & v[1] & v[2] & v[3] & v[4] & v[5] & v[6] & v[7]) == 0xffffffffu;
+  };
+  auto tally = [&](uint32_t b) {
     const uint32_t bit = 1u << (b & 31u);
     if (!(bm[b >> 5] & bit)) atomicOr(&bm[b >> 5], bit);
+  };
+  const uint64_t head = min((uint64_t)((16u - ((uint32_t)reinterpret_cast<uintptr_t>(img) & 15u)) & 15u), s.elems);
+  const uint64_t nvec = (s.elems - head) / 16;
+  const uint4* vec = reinterpret_cast<const uint4*>(img + head);
+  for (uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x; i < nvec; i += (uint64_t)gridDim.x * 256) {
+    if (full()) break;
+    const uint4 q = __ldg(vec + i);
+    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      tally(w[k] & 0xffu);
+      tally((w[k] >> 8) & 0xffu);
+      tally((w[k] >> 16) & 0xffu);
+      tally(w[k] >> 24);
+    }
+  }
+  if (blockIdx.x == 0) {                              // unaligned head and the < 16-byte tail
+    if (threadIdx.x < head) tally(__ldg(img + threadIdx.x));
+    const uint64_t t = head + nvec * 16 + threadIdx.x;
+    if (t < s.elems) tally(__ldg(img + t));
   }
   __syncthreads();
-  if (threadIdx.x < 8 && bm[threadIdx.x]) atomicOr(&bitmaps[img_local * 8 + threadIdx.x], bm[threadIdx.x]);
+  if (threadIdx.x < 8 && (bm[threadIdx.x] & ~seen)) atomicOr(gbm + threadIdx.x, bm[threadIdx.x]);
 }
 
 __global__ void k_poisson_vals(const uint32_t* bitmaps, float* vals, int n) {
@@ -37,7 +66,7 @@ __global__ void k_poisson_vals(const uint32_t* bitmaps, float* vals, int n) {
 cudaError_t launch_poisson_vals(const ImageSet& s, uint32_t* bitmaps, float* vals, int n_batch, cudaStream_t st) {
   cudaError_t e = cudaMemsetAsync(bitmaps, 0, sizeof(uint32_t) * 8 * n_batch, st);
   if (e != cudaSuccess) return e;
-  uint32_t bx = (uint32_t)((s.elems + 256 * 64 - 1) / (256 * 64));
+  uint32_t bx = (uint32_t)((s.elems + 256 * 16 * 8 - 1) / (256 * 16 * 8));   // 8 x 16-byte loads per thread
   if (bx < 1) bx = 1;
   k_unique_bitmap<<<dim3(bx, 1, s.count), 256, 0, st>>>(s, bitmaps);
   count_launch();

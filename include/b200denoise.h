@@ -154,7 +154,7 @@ int b2d_lab_convert(const uint8_t* d_in, uint8_t* d_out, size_t n_pixels, int di
 
 /* Test hook (host only, no GPU needed): the alias table of the generator-mode Poisson corruption
  * (skimage random_noise 'poisson', lib/roi_data_layer/minibatch.py:211-213) for vals = 2^log2_vals,
- * 0 <= log2_vals <= 8.  h_table[v * 256 + slot] = threshold | alias << 8: input byte v, 8 random
+ * 0 <= log2_vals <= 8.  h_table[v * 256 + slot] = alias | threshold << 8: input byte v, 8 random
  * bits pick the slot, 8 more are compared with the threshold (u < threshold keeps the slot's own
  * value, otherwise the alias is the output byte). */
 int b2d_poisson_table(int log2_vals, uint16_t* h_table);

@@ -117,7 +117,7 @@ def test_poisson_alias_table_represents_the_pmf(log2_vals):
     tab = np.zeros(65536, np.uint16)
     _lib.check(L.b2d_poisson_table(log2_vals, tab.ctypes.data_as(ctypes.c_void_p)))
     tab = tab.reshape(256, 256)
-    thr, alias = (tab & 0xff).astype(np.int64), (tab >> 8).astype(np.int64)
+    alias, thr = (tab & 0xff).astype(np.int64), (tab >> 8).astype(np.int64)
     vals = 1 << log2_vals
     k = np.arange(vals + 1)
     out_of_k = (255 * np.minimum(k, vals)) >> log2_vals
