@@ -8,14 +8,20 @@
 //   w       = space[i, j] * color_lut[|db| + |dg| + |dr|]          (lut: 766 floats)
 //   out_c   = round_half_even(sum(w * p_c) * (1 / sum(w)))
 //
-// Kernel (radius 4): CTA = 16 rows x 64 pixels, thread = 4 adjacent pixels.
-// The tile + apron lives in shared memory as four planes (b, g, r as fp32 and
-// the packed pixel) so that a thread's 12 neighbours of one tap row arrive in
-// 3 conflict-free LDS.128 per plane and are reused by its 4 outputs; the
-// colour distance is one VABSDIFF4 (packed SAD); the LUT sits in shared memory.
-// Compute bound: 49 taps x ~8 instructions per pixel (FP32/INT pipe roofline).
+// Kernel (radius 4): CTA = 16 rows x 64 pixels, thread = 4 adjacent pixels.  The first version kept
+// b / g / r as fp32 planes in shared memory and was bound by shared-memory wavefronts (ncu: LSU
+// data pipe 91 %, `mio_throttle` the top stall).  Now the tile holds only the packed pixel (4 B):
+//   * a neighbour's three floats are rebuilt in registers (PRMT onto 2^23, one FADD each) and
+//     shared by the up to 4 outputs of the thread that use it;
+//   * the spatial weight is folded into the colour LUT: r^2 takes 10 values inside the disc, so
+//     lut2[class][t] = space * lut[t] (the same fp32 product OpenCV forms per tap) costs one
+//     shared-memory load and no multiply;
+//   * the four accumulators of an output are two packed-fp32 pairs (b, g) and (r, weight sum),
+//     updated by two FFMA2 (`fma.rn.f32x2`, IEEE per lane: results identical to scalar code).
+// Per tap: VABSDIFF4, LEA, LDS, MOV, 2 x FFMA2 = 6 issue slots / 6 ALU-pipe cycles.
 #include "b2d_denoise.cuh"
 #include "b2d_plan.h"
+#include "b2d_noise.cuh"
 
 #include <cmath>
 
@@ -28,76 +34,94 @@ constexpr int BL_SH = BL_TH + 2 * BL_R;          // 24
 constexpr int BL_PLANE = BL_SW * BL_SH;          // 1728
 constexpr int BL_THREADS = (BL_TW / BL_PX) * BL_TH;   // 256
 constexpr int BL_LUT = 256 * 3;
+constexpr int BL_CLASSES = 10;                   // distinct i^2 + j^2 <= 16
+constexpr int BL_TILE_ITERS = (BL_PLANE + BL_THREADS - 1) / BL_THREADS;   // 7
 
-struct BilateralArgs {
-  float space[2 * BL_R + 1][2 * BL_R + 1];   // 0 outside the disc
-  const float* lut;                           // device, BL_LUT floats
-};
+__host__ __device__ constexpr int bl_class(int i, int j) {
+  const int r2 = i * i + j * j;
+  return r2 == 0 ? 0 : r2 == 1 ? 1 : r2 == 2 ? 2 : r2 == 4 ? 3 : r2 == 5 ? 4 : r2 == 8 ? 5 : r2 == 9 ? 6
+       : r2 == 10 ? 7 : r2 == 13 ? 8 : r2 == 16 ? 9 : -1;
+}
 
-__global__ void __launch_bounds__(BL_THREADS, 2) k_bilateral_r4(ImageSet s, BilateralArgs ba) {
-  extern __shared__ __align__(16) float sm[];
-  float* pb = sm;
-  float* pg = sm + BL_PLANE;
-  float* pr = sm + 2 * BL_PLANE;
-  uint32_t* pk = reinterpret_cast<uint32_t*>(sm + 3 * BL_PLANE);
-  float* lut = sm + 4 * BL_PLANE;
+__device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
+  unsigned long long v;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(v) : "f"(lo), "f"(hi));
+  return v;
+}
+__device__ __forceinline__ void fma2(unsigned long long& acc, unsigned long long a, unsigned long long b) {
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
+}
+
+__global__ void __launch_bounds__(BL_THREADS, 4) k_bilateral_r4(ImageSet s, const float* lut2g) {
+  extern __shared__ __align__(16) uint32_t smu[];
+  uint32_t* pk = smu;
+  float* lut2 = reinterpret_cast<float*>(smu + BL_PLANE);
 
   const int tid = threadIdx.x;
   const int img_local = image_of(s, blockIdx.z);
   const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
   const int x0 = blockIdx.x * BL_TW, y0 = blockIdx.y * BL_TH;
 
-  for (int i = tid; i < BL_LUT; i += BL_THREADS) lut[i] = ba.lut[i];
-  for (int i = tid; i < BL_PLANE; i += BL_THREADS) {
-    const int ty = i / BL_SW, tx = i - ty * BL_SW;
-    const int y = y0 + ty - BL_R, x = x0 + tx - BL_R;
-    uint32_t b = 0, g = 0, r = 0;
-    if (y >= 0 && y < s.h && x >= 0 && x < s.w) {
-      const uint8_t* p = img + ((uint64_t)y * s.w + x) * 3;
-      b = __ldg(p); g = __ldg(p + 1); r = __ldg(p + 2);
+  for (int i = tid; i < BL_CLASSES * BL_LUT / 4; i += BL_THREADS)
+    reinterpret_cast<float4*>(lut2)[i] = __ldg(reinterpret_cast<const float4*>(lut2g) + i);
+  {                                               // tile + apron: all loads in flight before the first store
+    uint32_t v[BL_TILE_ITERS][3];
+#pragma unroll
+    for (int k = 0; k < BL_TILE_ITERS; ++k) {
+      const int i = tid + k * BL_THREADS;
+      const int ty = i / BL_SW, tx = i - ty * BL_SW;
+      const int y = y0 + ty - BL_R, x = x0 + tx - BL_R;
+      const bool in = i < BL_PLANE && y >= 0 && y < s.h && x >= 0 && x < s.w;   // BORDER_CONSTANT: zeros take part
+      const uint8_t* p = img + (in ? ((uint64_t)y * s.w + x) * 3 : 0);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) v[k][c] = in ? (uint32_t)__ldg(p + c) : 0u;
     }
-    pb[i] = (float)b; pg[i] = (float)g; pr[i] = (float)r;
-    pk[i] = b | (g << 8) | (r << 16);
+#pragma unroll
+    for (int k = 0; k < BL_TILE_ITERS; ++k) {
+      const int i = tid + k * BL_THREADS;
+      if (i < BL_PLANE) pk[i] = v[k][0] | (v[k][1] << 8) | (v[k][2] << 16);
+    }
   }
   __syncthreads();
 
   const int tx = tid & 15, ty = tid >> 4;
   const int base = (ty + BL_R) * BL_SW + BL_PX * tx + BL_R;      // centre of output 0
   uint32_t ck[BL_PX];
-  float wsum[BL_PX], ab[BL_PX], ag[BL_PX], ar[BL_PX];
+  unsigned long long acc_bg[BL_PX], acc_rw[BL_PX];               // (sum w b, sum w g), (sum w r, sum w)
 #pragma unroll
   for (int p = 0; p < BL_PX; ++p) {
     ck[p] = pk[base + p];
-    wsum[p] = ab[p] = ag[p] = ar[p] = 0.0f;
+    acc_bg[p] = acc_rw[p] = 0ull;
   }
 #pragma unroll
   for (int i = -BL_R; i <= BL_R; ++i) {
-    const int rowoff = base + i * BL_SW - BL_R;                  // neighbour column jj = 0 .. 11
-    float nb[12], ng[12], nr[12];
+    const int rowoff = base + i * BL_SW - BL_R;                  // neighbour column jj = 0 .. 11, 16-byte aligned
     uint32_t nk[12];
 #pragma unroll
     for (int q = 0; q < 3; ++q) {
-      const float4 vb = *reinterpret_cast<const float4*>(pb + rowoff + 4 * q);
-      const float4 vg = *reinterpret_cast<const float4*>(pg + rowoff + 4 * q);
-      const float4 vr = *reinterpret_cast<const float4*>(pr + rowoff + 4 * q);
       const uint4 vk = *reinterpret_cast<const uint4*>(pk + rowoff + 4 * q);
-      nb[4 * q] = vb.x; nb[4 * q + 1] = vb.y; nb[4 * q + 2] = vb.z; nb[4 * q + 3] = vb.w;
-      ng[4 * q] = vg.x; ng[4 * q + 1] = vg.y; ng[4 * q + 2] = vg.z; ng[4 * q + 3] = vg.w;
-      nr[4 * q] = vr.x; nr[4 * q + 1] = vr.y; nr[4 * q + 2] = vr.z; nr[4 * q + 3] = vr.w;
       nk[4 * q] = vk.x; nk[4 * q + 1] = vk.y; nk[4 * q + 2] = vk.z; nk[4 * q + 3] = vk.w;
     }
 #pragma unroll
     for (int jj = 0; jj < 12; ++jj) {
+      bool used = false;
+#pragma unroll
+      for (int p = 0; p < BL_PX; ++p) {
+        const int j = jj - p - BL_R;
+        used = used || (j >= -BL_R && j <= BL_R && bl_class(i, j) >= 0);
+      }
+      if (!used) continue;
+      const unsigned long long n_bg = pack2(magic_byte<0>(nk[jj]) - 8388608.0f, magic_byte<1>(nk[jj]) - 8388608.0f);
+      const unsigned long long n_r1 = pack2(magic_byte<2>(nk[jj]) - 8388608.0f, 1.0f);
 #pragma unroll
       for (int p = 0; p < BL_PX; ++p) {
         const int j = jj - p - BL_R;                             // tap column offset for output p
-        if (j < -BL_R || j > BL_R || i * i + j * j > BL_R * BL_R) continue;
+        if (j < -BL_R || j > BL_R || bl_class(i, j) < 0) continue;
         const uint32_t t = __vsadu4(nk[jj], ck[p]);
-        const float w = ba.space[i + BL_R][j + BL_R] * lut[t];
-        wsum[p] += w;
-        ab[p] = fmaf(nb[jj], w, ab[p]);
-        ag[p] = fmaf(ng[jj], w, ag[p]);
-        ar[p] = fmaf(nr[jj], w, ar[p]);
+        const float w = lut2[bl_class(i, j) * BL_LUT + t];
+        const unsigned long long ww = pack2(w, w);
+        fma2(acc_bg[p], n_bg, ww);
+        fma2(acc_rw[p], n_r1, ww);
       }
     }
   }
@@ -106,10 +130,13 @@ __global__ void __launch_bounds__(BL_THREADS, 2) k_bilateral_r4(ImageSet s, Bila
   uint32_t o[12];
 #pragma unroll
   for (int p = 0; p < BL_PX; ++p) {
-    const float inv = 1.0f / wsum[p];
-    o[3 * p] = (uint32_t)__float2int_rn(ab[p] * inv);
-    o[3 * p + 1] = (uint32_t)__float2int_rn(ag[p] * inv);
-    o[3 * p + 2] = (uint32_t)__float2int_rn(ar[p] * inv);
+    float ab, ag, ar, wsum;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(ab), "=f"(ag) : "l"(acc_bg[p]));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(ar), "=f"(wsum) : "l"(acc_rw[p]));
+    const float inv = 1.0f / wsum;
+    o[3 * p] = (uint32_t)__float2int_rn(ab * inv);
+    o[3 * p + 1] = (uint32_t)__float2int_rn(ag * inv);
+    o[3 * p + 2] = (uint32_t)__float2int_rn(ar * inv);
   }
   uint8_t* op = s.out + (uint64_t)img_local * s.elems + ((uint64_t)y * s.w + x) * 3;
   if (x + BL_PX <= s.w && (reinterpret_cast<uintptr_t>(op) & 3u) == 0) {
@@ -156,12 +183,15 @@ __global__ void __launch_bounds__(256) k_bilateral_any(ImageSet s, int radius, c
   }
 }
 
-// host: OpenCV's tables.  ws layout: [lut 768 floats][space (2r+1)^2 floats]
+// host: OpenCV's tables.  ws layout: [lut 768 floats][space (2r+1)^2 floats][pad][lut2 10 x 768 floats (r = 4)]
 int run_bilateral(const b2d_spec& sp, const ImageSet& s, uint8_t* ws_tables, cudaStream_t st) {
   const int radius = sp.d / 2, d = 2 * radius + 1;
   const double gc = -0.5 / ((double)sp.sigma_color * sp.sigma_color);
   const double gs = -0.5 / ((double)sp.sigma_space * sp.sigma_space);
-  float host[BL_LUT + 15 * 15];
+  constexpr int kLut2Off = BL_LUT + 15 * 15 + 31;                // floats; 16-byte aligned (1024)
+  static_assert(kLut2Off % 4 == 0, "lut2 must be float4 aligned");
+  float host[kLut2Off + BL_CLASSES * BL_LUT];
+  for (int i = 0; i < kLut2Off + BL_CLASSES * BL_LUT; ++i) host[i] = 0.0f;
   for (int i = 0; i < BL_LUT; ++i) host[i] = (float)std::exp((double)i * i * gc);
   for (int i = -radius; i <= radius; ++i)
     for (int j = -radius; j <= radius; ++j) {
@@ -169,21 +199,26 @@ int run_bilateral(const b2d_spec& sp, const ImageSet& s, uint8_t* ws_tables, cud
       host[BL_LUT + (i + radius) * d + j + radius] = r > radius ? 0.0f : (float)std::exp(r * r * gs);
     }
   float* dtab = reinterpret_cast<float*>(ws_tables);
-  cudaError_t e = cudaMemcpyAsync(dtab, host, sizeof(float) * (BL_LUT + d * d), cudaMemcpyHostToDevice, st);
+  if (radius == BL_R)
+    for (int i = -BL_R; i <= BL_R; ++i)
+      for (int j = -BL_R; j <= BL_R; ++j) {
+        const int c = bl_class(i, j);
+        if (c < 0) continue;
+        const float sw = host[BL_LUT + (i + radius) * d + j + radius];
+        for (int t = 0; t < BL_LUT; ++t) host[kLut2Off + c * BL_LUT + t] = sw * host[t];   // fp32 product, as per tap
+      }
+  const size_t nfl = radius == BL_R ? (size_t)kLut2Off + BL_CLASSES * BL_LUT : (size_t)BL_LUT + d * d;
+  cudaError_t e = cudaMemcpyAsync(dtab, host, sizeof(float) * nfl, cudaMemcpyHostToDevice, st);
   if (e != cudaSuccess) return fail_cuda(e, "bilateral tables");
   if (radius == BL_R) {
-    BilateralArgs ba;
-    for (int i = 0; i < d; ++i)
-      for (int j = 0; j < d; ++j) ba.space[i][j] = host[BL_LUT + i * d + j];
-    ba.lut = dtab;
-    const size_t smem = sizeof(float) * (4 * BL_PLANE + BL_LUT);
+    const size_t smem = sizeof(uint32_t) * BL_PLANE + sizeof(float) * BL_CLASSES * BL_LUT;
     static bool attr_set = false;
     if (!attr_set) {
       cudaFuncSetAttribute(k_bilateral_r4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       attr_set = true;
     }
     const dim3 grid((s.w + BL_TW - 1) / BL_TW, (s.h + BL_TH - 1) / BL_TH, s.count);
-    k_bilateral_r4<<<grid, BL_THREADS, smem, st>>>(s, ba);
+    k_bilateral_r4<<<grid, BL_THREADS, smem, st>>>(s, dtab + kLut2Off);
   } else {
     const uint64_t npix = (uint64_t)s.h * s.w;
     uint32_t bx = (uint32_t)std::min<uint64_t>((npix + 255) / 256, 148u * 16u);

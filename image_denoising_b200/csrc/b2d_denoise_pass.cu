@@ -8,7 +8,7 @@ namespace b2d {
 cudaError_t launch_median_k(const ImageSet& s, int k, cudaStream_t st);
 int run_bilateral(const b2d_spec& sp, const ImageSet& s, uint8_t* ws_tables, cudaStream_t st);
 
-constexpr size_t kBilateralTableBytes = sizeof(float) * (768 + 15 * 15 + 31);
+constexpr size_t kBilateralTableBytes = sizeof(float) * (768 + 15 * 15 + 31 + 10 * 768);   // lut, space, pad, lut2
 
 size_t denoise_workspace_bytes(const b2d_plan& p) {
   size_t extra = 0;
