@@ -12,6 +12,8 @@
 #include "b2d_denoise.cuh"
 #include "b2d_plan.h"
 
+#include <cstdlib>
+
 namespace b2d {
 
 constexpr int MD_THREADS = 256;
@@ -128,6 +130,124 @@ __global__ void __launch_bounds__(MD_THREADS) k_median(ImageSet s) {
   }
 }
 
+// ---------------------------------------------------------------------------
+// Two horizontally adjacent outputs at a time (a "shared partial sort").  For 7 x 7 the windows of
+// pixels x and x + 1 share 6 columns = 42 values.  A value of the shared set with >= 25 shared
+// values above (below) it cannot be the median (rank 25 of 49) of either window, so forgetful
+// selection first strips the 17 smallest and 17 largest shared values (start with 26 candidates,
+// drop min and max, insert the next value, ...); the median of a window is then the median of
+// the 8 survivors and its own private column (15 values).  ~262 compare-exchanges per output
+// instead of 471 (5 x 5: 20 shared -> 6 survivors + 5 private, ~79 instead of 126).  A thread owns 4 pixels: lane 0 of a u16x2 word works on the pair
+// (x, x + 1), lane 1 on (x + 2, x + 3) of the same channel, i.e. two bytes 6 apart.
+constexpr int M7_THREADS = 128;
+constexpr int M7_TILE_WB = M7_THREADS * 12;        // 4 pixels per thread
+constexpr int M7_TILE_H = 16;
+constexpr int M7_APRON = 12;                       // >= 9 bytes to the left, 9 + 6 - ... to the right; multiple of 4
+constexpr int M7_SROW = M7_TILE_WB + 2 * M7_APRON;
+
+// strip min and max of a[0..M) while values remain to be inserted; ends with M = 2 CAP - N, then one more strip:
+// survivors a[1 .. 2 CAP - N - 2]
+template <int M, int CAP, int N>
+struct Strip {
+  template <class Get>
+  static __device__ __forceinline__ void run(uint32_t (&a)[CAP], Get get) {
+    minmax<M, CAP>(a);
+    if constexpr (M > 2 * CAP - N) {
+      a[0] = get(N - (M - (2 * CAP - N)));         // values CAP .. N-1 in order
+      Strip<M - 1, CAP, N>::run(a, get);
+    }
+  }
+};
+
+template <int K>
+__global__ void __launch_bounds__(M7_THREADS) k_median_pairs(ImageSet s) {
+  constexpr int R = K / 2, N = K * K, NS = (K - 1) * K;      // window, shared values of a pair
+  constexpr int CAP = (N + 1) / 2 + 1;                        // 26 (K = 7), 14 (K = 5)
+  constexpr int KEEP = 2 * CAP - NS - 2;                      // 8, 6 survivors
+  constexpr int CAP2 = KEEP + 1, N2 = KEEP + K;               // median of 15 / 11
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int tid = threadIdx.x;
+  const int c0 = blockIdx.x * M7_TILE_WB, y0 = blockIdx.y * M7_TILE_H;
+  const int img_local = image_of(s, blockIdx.z);
+  const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
+  const int rows = M7_TILE_H + 2 * R;
+  static_assert(3 * R <= M7_APRON && 3 * (R + 1) + 2 + 6 <= 11 + M7_APRON, "apron too small");
+
+  for (int it = tid; it < rows * (M7_SROW / 4); it += M7_THREADS) {
+    const int tr = it / (M7_SROW / 4), wc = it - tr * (M7_SROW / 4);
+    const int y = min(max(y0 - R + tr, 0), s.h - 1);
+    const uint8_t* row = img + (uint64_t)y * s.rowbytes;
+    const int c = c0 - M7_APRON + 4 * wc;
+    uint32_t w;
+    if (c >= 0 && c + 4 <= s.rowbytes && ((reinterpret_cast<uintptr_t>(row + c) & 3u) == 0)) {
+      w = __ldg(reinterpret_cast<const uint32_t*>(row + c));
+    } else {                                        // REPLICATE: clamp the pixel, keep the channel
+      uint32_t b[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int cc = c + k;
+        int px = cc >= 0 ? cc / 3 : -((-cc + 2) / 3);
+        const int ch = cc - 3 * px;
+        px = min(max(px, 0), s.w - 1);
+        b[k] = __ldg(row + px * 3 + ch);
+      }
+      w = pack4(b[0], b[1], b[2], b[3]);
+    }
+    *reinterpret_cast<uint32_t*>(smem + tr * M7_SROW + 4 * wc) = w;
+  }
+  __syncthreads();
+
+  const int c = c0 + 12 * tid;
+  if (c >= s.rowbytes) return;
+  const uint8_t* sp = smem + M7_APRON + 12 * tid;
+  const int nrows = min(M7_TILE_H, s.h - y0);
+  for (int r = 0; r < nrows; ++r) {
+    const uint8_t* rp = sp + r * M7_SROW;
+    uint32_t L[3], Rt[3];                           // per channel: (px0, px2) and (px1, px3) medians
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      // value of window row dy, pixel column d (relative to px0 / px2), channel k as (lane0, lane1)
+      auto at = [&](int dy, int d) {
+        const uint8_t* q = rp + dy * M7_SROW + 3 * d + k;
+        return __byte_perm((uint32_t)q[0], (uint32_t)q[6], 0x5410);
+      };
+      auto shared = [&](int e) { return at(e / (K - 1), e % (K - 1) - (R - 1)); };   // columns -(R-1) .. R
+      uint32_t a[CAP];
+#pragma unroll
+      for (int e = 0; e < CAP; ++e) a[e] = shared(e);
+      Strip<CAP, CAP, NS>::run(a, shared);          // survivors a[1 .. KEEP]
+      uint32_t bl[CAP2], br[CAP2];
+#pragma unroll
+      for (int e = 0; e < KEEP; ++e) bl[e] = br[e] = a[1 + e];
+      bl[KEEP] = at(0, -R);
+      br[KEEP] = at(0, R + 1);
+      L[k] = Forget<CAP2, CAP2, N2>::run(bl, [&](int e) { return at(e - KEEP, -R); });
+      Rt[k] = Forget<CAP2, CAP2, N2>::run(br, [&](int e) { return at(e - KEEP, R + 1); });
+    }
+    // bytes: px0 = (L0.lo, L1.lo, L2.lo), px1 = (R*.lo), px2 = (L*.hi), px3 = (R*.hi)
+    const uint32_t w0 = __byte_perm(__byte_perm(L[0], L[1], 0x0040), __byte_perm(L[2], Rt[0], 0x0040), 0x5410);
+    const uint32_t w1 = __byte_perm(__byte_perm(Rt[1], Rt[2], 0x0040), __byte_perm(L[0], L[1], 0x0062), 0x5410);
+    const uint32_t w2 = __byte_perm(__byte_perm(L[2], Rt[0], 0x0062), __byte_perm(Rt[1], Rt[2], 0x0062), 0x5410);
+    uint8_t* op = s.out + (uint64_t)img_local * s.elems + (uint64_t)(y0 + r) * s.rowbytes + c;
+    if (c + 12 <= s.rowbytes && (reinterpret_cast<uintptr_t>(op) & 3u) == 0) {
+      uint32_t* ow = reinterpret_cast<uint32_t*>(op);
+      ow[0] = w0; ow[1] = w1; ow[2] = w2;
+    } else {
+      const uint32_t w[3] = {w0, w1, w2};
+      for (int b = 0; b < 12 && c + b < s.rowbytes; ++b) op[b] = (uint8_t)(w[b >> 2] >> (8 * (b & 3)));
+    }
+  }
+}
+
+template <int K>
+static cudaError_t launch_median_pairs(const ImageSet& s, cudaStream_t st) {
+  const dim3 grid((s.rowbytes + M7_TILE_WB - 1) / M7_TILE_WB, (s.h + M7_TILE_H - 1) / M7_TILE_H, s.count);
+  const size_t smem = (size_t)(M7_TILE_H + 2 * (K / 2)) * M7_SROW;
+  k_median_pairs<K><<<grid, M7_THREADS, smem, st>>>(s);
+  count_launch();
+  return cudaGetLastError();
+}
+
 template <int K>
 static cudaError_t launch_median_t(const ImageSet& s, cudaStream_t st) {
   const dim3 grid((s.rowbytes + MD_TILE_WB - 1) / MD_TILE_WB, (s.h + MD_TILE_H - 1) / MD_TILE_H, s.count);
@@ -139,8 +259,10 @@ static cudaError_t launch_median_t(const ImageSet& s, cudaStream_t st) {
 
 cudaError_t launch_median_k(const ImageSet& s, int k, cudaStream_t st) {
   if (s.count <= 0) return cudaSuccess;
-  if (k == 5) return launch_median_t<5>(s, st);
-  if (k == 7) return launch_median_t<7>(s, st);
+  // B2D_MEDIAN_SINGLE=1 selects the one-output-at-a-time kernels (measurement knob)
+  static const bool single = [] { const char* e = getenv("B2D_MEDIAN_SINGLE"); return e && e[0] == '1'; }();
+  if (k == 5) return single ? launch_median_t<5>(s, st) : launch_median_pairs<5>(s, st);
+  if (k == 7) return single ? launch_median_t<7>(s, st) : launch_median_pairs<7>(s, st);
   return cudaErrorInvalidValue;
 }
 
