@@ -7,6 +7,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 
 using namespace b2d;
 
@@ -214,8 +215,12 @@ extern "C" int b2d_run_host(b2d_plan* plan, const uint8_t* h_in, uint8_t* h_out,
     for (int i = 0; i < 3; ++i) CK(cudaStreamCreateWithFlags(&plan->h_streams[i], cudaStreamNonBlocking));
     plan->h_ready = true;
   }
-  // chunks of >= 32 MiB (at least one image) so each copy runs at full PCIe rate
-  int per = (int)std::max<uint64_t>(1, (32ull << 20) / plan->elems);
+  // chunks of >= 32 MiB (at least one image) so each copy runs at full PCIe rate (B2D_HOST_CHUNK_MB: tuning knob)
+  static const uint64_t chunk_bytes = [] {
+    const char* e = getenv("B2D_HOST_CHUNK_MB");
+    return (uint64_t)(e && atoi(e) > 0 ? atoi(e) : 32) << 20;
+  }();
+  int per = (int)std::max<uint64_t>(1, chunk_bytes / plan->elems);
   bool shared_ws = plan->need_aux;    // pre-pass / wavelet workspaces are shared by the whole batch: keep one chunk
   for (const SpecGroup& g : plan->groups) shared_ws = shared_ws || g.spec.denoise == B2D_DENOISE_WAVELET;
   if (shared_ws) per = plan->n;
