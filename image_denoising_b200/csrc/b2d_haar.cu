@@ -398,8 +398,21 @@ int run_haar(const b2d_plan& p, const ImageSet& s, int kind, const NoiseArgs& na
   }
   for (int first = 0; first < s.count; first += chunk) {
     const int cnt = std::min(chunk, s.count - first);
-    // two resident CTAs per SM over the whole chunk; at least one wave per image for small batches
-    const int per_image = std::max(1, std::min((hg.total_strips + 7) / 8, std::max(1, 2 * sms * 4 / cnt)));
+    // two resident CTAs per SM: pick the CTA count per image that fills whole waves (cnt x per_image close to a
+    // multiple of 2 x SMs), at least 2 waves' worth, at most one strip row of 8 warps per CTA
+    const int max_pi = std::max(1, (hg.total_strips + 7) / 8);
+    const int slots = 2 * sms;
+    int per_image = std::min(max_pi, std::max(1, (2 * slots + cnt - 1) / cnt));
+    {
+      double best = -1.0;
+      int best_pi = per_image;
+      for (int c = per_image; c <= std::min(max_pi, per_image + 64); ++c) {
+        const long total = (long)c * cnt;
+        const double fill = (double)total / (double)(((total + slots - 1) / slots) * slots);
+        if (fill > best + 0.02) { best = fill; best_pi = c; }
+      }
+      per_image = best_pi;
+    }
     const dim3 grid((unsigned)per_image, (unsigned)cnt, 1);
     wavelet_stats_begin(stats, hist, cnt * 3, st);
     int rc = dispatch_haar(kind, 0, grid, st, s, na, hg, dd1, stats, fa, first);
