@@ -78,13 +78,59 @@ def _get_image_blob(roidb, scale_inds, double_filter=False):
     return im_list_to_blob(processed_ims), im_scales
 
 
-def get_minibatch(roidb, num_classes):
-    """Given a roidb, construct a minibatch sampled from it (minibatch.py:42-75)."""
+def _get_image_blob_device(roidb, scale_inds, double_filter=False):
+    """`_get_image_blob` with every step after the decode on the GPU: one H2D copy of
+    the uint8 images, corrupt -> denoise (`b2d_run`), flip + mean subtraction + bilinear resize + NHWC
+    packing (`b2d_blob_prep`).  Returns (blob: (N, Hmax, Wmax, 3) float32 CUDA tensor, im_scales)."""
+    import torch
+    from .blob import blob_shape, prep_blob_device
+    imgs = [_load(r) for r in roidb]
+    specs = [resolve_mix(r.get('noise_type', 'original'), "train", None) for r in roidb]
+    indices = [int(r.get('index', i)) for i, r in enumerate(roidb)]
+    targets = [cfg.TRAIN.SCALES[scale_inds[i]] for i in range(len(roidb))]
+    shapes = [blob_shape(im.shape[0], im.shape[1], targets[i], cfg.TRAIN.MAX_SIZE) for i, im in enumerate(imgs)]
+    hmax, wmax = max(s[1] for s in shapes), max(s[2] for s in shapes)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    blob = torch.empty((len(imgs), hmax, wmax, 3), dtype=torch.float32, device=dev)
+    groups = {}
+    for i, im in enumerate(imgs):
+        groups.setdefault((im.shape, targets[i]), []).append(i)
+    for (shape, target), idx in groups.items():
+        batch = torch.from_numpy(np.ascontiguousarray(np.stack([imgs[i] for i in idx]))).to(dev)
+        consecutive = all(indices[idx[j]] == indices[idx[0]] + j for j in range(len(idx)))
+        if consecutive:
+            res = api.apply(batch, [specs[i] for i in idx], seed=cfg.RNG_SEED, first_index=indices[idx[0]])
+        else:
+            res = torch.cat([api.apply(batch[j:j + 1], specs[i], seed=cfg.RNG_SEED, first_index=indices[i])
+                             for j, i in enumerate(idx)])
+        if double_filter:
+            for j, i in enumerate(idx):
+                post = next((d for d in POST_DENOISE_ORDER if d in specs[i]), None)
+                if post:
+                    res[j:j + 1] = api.apply(res[j:j + 1].contiguous(), "original_" + post)
+        flips = [bool(roidb[i].get('flipped', False)) for i in idx]
+        whole = idx == list(range(idx[0], idx[0] + len(idx)))
+        if whole:                                              # the group is a contiguous slab of the blob
+            prep_blob_device(res, cfg.PIXEL_MEANS, target, cfg.TRAIN.MAX_SIZE, flipped=flips,
+                             out=blob[idx[0]:idx[0] + len(idx)])
+        else:
+            for j, i in enumerate(idx):
+                prep_blob_device(res[j:j + 1], cfg.PIXEL_MEANS, target, cfg.TRAIN.MAX_SIZE, flipped=flips[j:j + 1],
+                                 out=blob[i:i + 1])
+    return blob, [s[0] for s in shapes]
+
+
+def get_minibatch(roidb, num_classes, device_blob=False):
+    """Given a roidb, construct a minibatch sampled from it (minibatch.py:42-75).
+    device_blob=True keeps blobs['data'] on the GPU (built by `_get_image_blob_device`)."""
     num_images = len(roidb)
     random_scale_inds = npr.randint(0, high=len(cfg.TRAIN.SCALES), size=num_images)
     assert cfg.TRAIN.BATCH_SIZE % num_images == 0, \
         'num_images ({}) must divide BATCH_SIZE ({})'.format(num_images, cfg.TRAIN.BATCH_SIZE)
-    im_blob, im_scales = _get_image_blob(roidb, random_scale_inds)
+    if device_blob:
+        im_blob, im_scales = _get_image_blob_device(roidb, random_scale_inds)
+    else:
+        im_blob, im_scales = _get_image_blob(roidb, random_scale_inds)
     blobs = {'data': im_blob}
     assert len(im_scales) == 1, "Single batch only"
     assert len(roidb) == 1, "Single batch only"

@@ -159,6 +159,23 @@ int b2d_lab_convert(const uint8_t* d_in, uint8_t* d_out, size_t n_pixels, int di
  * value, otherwise the alias is the output byte). */
 int b2d_poisson_table(int log2_vals, uint16_t* h_table);
 
+/* ---- next stage: the network input blob, on the device ------------------------
+ * b2d_blob_shape: geometry of prep_im_for_blob (lib/utils/blob.py:37-45) for an h x w image:
+ *   im_scale = target_size / min(h, w), capped so that round(im_scale * max(h, w)) <= max_size;
+ *   out_h, out_w = cv2.resize's dsize = (cvRound(h * im_scale), cvRound(w * im_scale)).  Host only.
+ * b2d_blob_prep: d_out[i] (blob_h x blob_w x 3 float32, zero padded like im_list_to_blob,
+ *   blob.py:17-30) = cv2.resize(d_in[i].astype(float32) - pixel_means, fx = fy = im_scale,
+ *   INTER_LINEAR) (blob.py:35,43-44); d_flip[i] != 0 mirrors image i horizontally first
+ *   (lib/roi_data_layer/minibatch.py:1676-1677).  d_in: n x h x w x 3 uint8; d_flip: n bytes on the
+ *   device or NULL; pixel_means: 3 host doubles (cfg.PIXEL_MEANS, lib/model/config.py:252).
+ *   flags: B2D_BLOB_F32_COORDS = interpolation fractions from the float32 source coordinate, bit-exact with
+ *   OpenCV's own C++ resize (cv2.setUseOptimized(False)); 0 = double-precision coordinate, which is what the
+ *   IPP-backed cv2 wheels return (they differ from the former by up to 4e-5 relative on downscales). */
+#define B2D_BLOB_F32_COORDS 1
+int b2d_blob_shape(int h, int w, int target_size, int max_size, double* im_scale, int* out_h, int* out_w);
+int b2d_blob_prep(const uint8_t* d_in, int n, int h, int w, float* d_out, int blob_h, int blob_w,
+                  double im_scale, const double* pixel_means, const uint8_t* d_flip, int flags, void* cuda_stream);
+
 /* Per-image result statistics gathered after the run (8(e): the only data
  * that ever crosses GPUs): checksum = sum of bytes * (1 + index mod 251)
  * mod 2^64 of d_out[i]; sse = sum (d_out - d_ref)^2 (for PSNR vs clean). */

@@ -136,3 +136,18 @@ def test_poisson_alias_table_represents_the_pmf(log2_vals):
         assert mean_err < 2e-3, (log2_vals, v, mean_err)
     with pytest.raises(_lib.B2DError):
         _lib.check(L.b2d_poisson_table(9, tab.ctypes.data_as(ctypes.c_void_p)))
+
+
+def test_blob_shape_matches_host_mirror():
+    """b2d_blob_shape (host code of the library) == the scale / dsize of the reference's
+    prep_im_for_blob through cv2.resize (lib/utils/blob.py:37-45), over many image sizes."""
+    from image_denoising_b200 import blob
+    rng = np.random.RandomState(4)
+    shapes = [(600, 1000), (375, 500), (333, 500), (500, 375), (480, 640), (1080, 1920), (2048, 2048), (301, 333),
+              (64, 96), (1000, 200)] + [(int(a), int(b)) for a, b in rng.randint(40, 1400, size=(60, 2))]
+    means = np.array([[[102.9801, 115.9465, 122.7717]]])
+    for h, w in shapes:
+        for target, mx in ((600, 1000), (800, 1333), (224, 224)):
+            im, s_ref = blob.prep_im_for_blob(np.zeros((h, w, 3), np.uint8), means, target, mx)
+            s, oh, ow = blob.blob_shape(h, w, target, mx)
+            assert s == s_ref and (oh, ow) == im.shape[:2], (h, w, target, mx, s, s_ref, (oh, ow), im.shape)
