@@ -40,3 +40,23 @@ def get_test_blob(im):
                                         interpolation=cv2.INTER_LINEAR))
         im_scale_factors.append(im_scale)
     return im_list_to_blob(processed_ims), np.array(im_scale_factors)
+
+
+def get_test_blob_device(batch):
+    """test.py:49-83 for a device batch (N, H, W, 3) uint8 (the output of `corrupt_batch_for_test` kept
+    on the GPU): blob (N * len(TEST.SCALES), Hmax, Wmax, 3) float32 CUDA tensor + the scale factors.
+    Scale s of image i is blob[i * len(SCALES) + s], the order `_get_image_blob` gives for one image."""
+    import torch
+    from .blob import blob_shape, prep_blob_device
+    n, h, w, _ = batch.shape
+    shapes = [blob_shape(h, w, t, cfg.TEST.MAX_SIZE) for t in cfg.TEST.SCALES]
+    hmax, wmax, ns = max(s[1] for s in shapes), max(s[2] for s in shapes), len(shapes)
+    blob = torch.empty((n, ns, hmax, wmax, 3), dtype=torch.float32, device=batch.device)
+    for k, target in enumerate(cfg.TEST.SCALES):
+        if ns == 1:
+            prep_blob_device(batch, cfg.PIXEL_MEANS, target, cfg.TEST.MAX_SIZE, out=blob.view(n, hmax, wmax, 3))
+        else:
+            tmp = torch.empty((n, hmax, wmax, 3), dtype=torch.float32, device=batch.device)
+            prep_blob_device(batch, cfg.PIXEL_MEANS, target, cfg.TEST.MAX_SIZE, out=tmp)
+            blob[:, k] = tmp
+    return blob.view(n * ns, hmax, wmax, 3), np.array([s[0] for s in shapes])

@@ -116,3 +116,13 @@ def test_minibatch_device_blob_equals_host_path(cuda):
     b = minibatch.get_minibatch(roidb[:1], 21, device_blob=True)
     assert b['data'].is_cuda and np.array_equal(a['gt_boxes'], b['gt_boxes']) and np.array_equal(a['im_info'], b['im_info'])
     check(b['data'].cpu().numpy(), a['data'])
+
+
+def test_test_side_blob_device(cuda):
+    from image_denoising_b200 import test_hook
+    batch = synth_batch(2, 375, 500, seed=11, kind="smooth")
+    dev, scales = test_hook.get_test_blob_device(torch.from_numpy(batch).to(cuda))
+    for i in range(2):
+        want, s_ref = test_hook.get_test_blob(batch[i])
+        assert np.array_equal(scales, s_ref)
+        check(dev[i * len(scales):(i + 1) * len(scales)].cpu().numpy(), want)
