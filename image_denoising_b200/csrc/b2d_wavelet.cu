@@ -21,11 +21,13 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 
 namespace b2d {
 
 // ---------------------------------------------------------------- geometry --
-static const double kS = 0.7071067811865476, kC1 = 0.01657281518405971, kC2 = 0.12153397801643787;
+constexpr double kSd = 0.7071067811865476, kC1d = 0.01657281518405971, kC2d = 0.12153397801643787;
+static const double kS = kSd, kC1 = kC1d, kC2 = kC2d;
 
 void wavelet_geometry(WvGeom& g, int wavelet, int levels_req, int h, int w) {
   g.F = wavelet == B2D_WAVELET_DB1 ? 2 : 10;
@@ -187,6 +189,182 @@ __global__ void __launch_bounds__(256) k_dwt_cols(WvGeom g, float* ws, int level
       s_dd = __fadd_rn(s_dd, __fmul_rn(g.dec_hi[j], hv));
     }
     aa[t] = s_aa; da[t] = s_da; ad[t] = s_ad; dd[t] = s_dd;
+  }
+}
+
+// ---- specialised versions (the ones that run): filter taps are compile-time constants, zero taps
+// (8 of the 10 in bior1.5's dec_hi / rec_lo) cost nothing, a thread produces 4 consecutive outputs
+// along the filtered axis from a register window (F + 6 inputs instead of 4 F), 2-D grids (no
+// integer division).  Accumulation order per output is that of the generic kernels above, which
+// stay as the executable definition (B2D_WV_GENERIC=1 runs them; the tests compare both).
+template <int WAVE> struct WvCoef;
+template <> struct WvCoef<B2D_WAVELET_DB1> {
+  static constexpr int F = 2;
+  static __host__ __device__ constexpr float dec_lo(int j) { return (float)kSd; }
+  static __host__ __device__ constexpr float dec_hi(int j) { return j == 0 ? -(float)kSd : (float)kSd; }
+  static __host__ __device__ constexpr float rec_lo(int j) { return (float)kSd; }
+  static __host__ __device__ constexpr float rec_hi(int j) { return j == 0 ? (float)kSd : -(float)kSd; }
+};
+template <> struct WvCoef<B2D_WAVELET_BIOR15> {
+  static constexpr int F = 10;
+  static __host__ __device__ constexpr float dec_lo(int j) {
+    return j == 0 ? (float)kC1d : j == 1 ? -(float)kC1d : j == 2 ? -(float)kC2d : j == 3 ? (float)kC2d : j == 4 ? (float)kSd
+         : j == 5 ? (float)kSd : j == 6 ? (float)kC2d : j == 7 ? -(float)kC2d : j == 8 ? -(float)kC1d : (float)kC1d;
+  }
+  static __host__ __device__ constexpr float dec_hi(int j) { return j == 4 ? -(float)kSd : j == 5 ? (float)kSd : 0.0f; }
+  static __host__ __device__ constexpr float rec_lo(int j) { return j == 4 || j == 5 ? (float)kSd : 0.0f; }
+  static __host__ __device__ constexpr float rec_hi(int j) {
+    return j == 0 ? (float)kC1d : j == 1 ? (float)kC1d : j == 2 ? -(float)kC2d : j == 3 ? -(float)kC2d : j == 4 ? (float)kSd
+         : j == 5 ? -(float)kSd : j == 6 ? (float)kC2d : j == 7 ? (float)kC2d : j == 8 ? -(float)kC1d : -(float)kC1d;
+  }
+};
+constexpr int WV_RO = 4;                                       // outputs per thread along the filtered axis
+
+template <int WAVE>
+__global__ void __launch_bounds__(256) k_dwt_rows_t(WvGeom g, float* ws, int level, size_t in_off) {
+  using C = WvCoef<WAVE>;
+  constexpr int F = C::F, NIN = F + 2 * (WV_RO - 1);
+  const int w = g.w[level - 1], wo = g.w[level], y = blockIdx.y;
+  const int i0 = (blockIdx.x * 256 + threadIdx.x) * WV_RO;
+  if (i0 >= wo) return;
+  float* base = ws + (size_t)blockIdx.z * g.chan_floats;
+  const float* row = base + in_off + (size_t)y * w;
+  const int xlo = 2 * i0 + 2 - F;                              // x[2 i + 1 - j], j = 0 .. F-1, i = i0 .. i0 + 3
+  float v[NIN];
+  if (xlo >= 0 && xlo + NIN <= w) {
+#pragma unroll
+    for (int e = 0; e < NIN; ++e) v[e] = row[xlo + e];
+  } else {
+#pragma unroll
+    for (int e = 0; e < NIN; ++e) v[e] = row[sym_ext(xlo + e, w)];
+  }
+  float* lo = base + g.off_tlo + (size_t)y * wo;
+  float* hi = base + g.off_thi + (size_t)y * wo;
+#pragma unroll
+  for (int o = 0; o < WV_RO; ++o) {
+    if (i0 + o >= wo) break;
+    float a = 0.f, d = 0.f;
+#pragma unroll
+    for (int j = 0; j < F; ++j) {
+      const float x = v[2 * o + F - 1 - j];
+      if (C::dec_lo(j) != 0.0f) a = __fadd_rn(a, __fmul_rn(C::dec_lo(j), x));
+      if (C::dec_hi(j) != 0.0f) d = __fadd_rn(d, __fmul_rn(C::dec_hi(j), x));
+    }
+    lo[i0 + o] = a;
+    hi[i0 + o] = d;
+  }
+}
+
+template <int WAVE>
+__global__ void __launch_bounds__(256) k_dwt_cols_t(WvGeom g, float* ws, int level) {
+  using C = WvCoef<WAVE>;
+  constexpr int F = C::F, NIN = F + 2 * (WV_RO - 1);
+  const int h = g.h[level - 1], wo = g.w[level], ho = g.h[level];
+  const int x = blockIdx.x * 256 + threadIdx.x, i0 = blockIdx.y * WV_RO;
+  if (x >= wo) return;
+  float* base = ws + (size_t)blockIdx.z * g.chan_floats;
+  const float* lo = base + g.off_tlo + x;
+  const float* hi = base + g.off_thi + x;
+  const int ylo = 2 * i0 + 2 - F;
+  float vl[NIN], vh[NIN];
+  const bool inside = ylo >= 0 && ylo + NIN <= h;
+#pragma unroll
+  for (int e = 0; e < NIN; ++e) {
+    const int yy = inside ? ylo + e : sym_ext(ylo + e, h);
+    vl[e] = lo[(size_t)yy * wo];
+    vh[e] = hi[(size_t)yy * wo];
+  }
+  float* aa = base + g.off_app[level] + x;
+  float* da = base + g.off_det[level][0] + x;
+  float* ad = base + g.off_det[level][1] + x;
+  float* dd = base + g.off_det[level][2] + x;
+#pragma unroll
+  for (int o = 0; o < WV_RO; ++o) {
+    if (i0 + o >= ho) break;
+    float s_aa = 0.f, s_da = 0.f, s_ad = 0.f, s_dd = 0.f;
+#pragma unroll
+    for (int j = 0; j < F; ++j) {
+      const float l = vl[2 * o + F - 1 - j], hv = vh[2 * o + F - 1 - j];
+      if (C::dec_lo(j) != 0.0f) { s_aa = __fadd_rn(s_aa, __fmul_rn(C::dec_lo(j), l)); s_ad = __fadd_rn(s_ad, __fmul_rn(C::dec_lo(j), hv)); }
+      if (C::dec_hi(j) != 0.0f) { s_da = __fadd_rn(s_da, __fmul_rn(C::dec_hi(j), l)); s_dd = __fadd_rn(s_dd, __fmul_rn(C::dec_hi(j), hv)); }
+    }
+    const size_t r = (size_t)(i0 + o) * wo;
+    aa[r] = s_aa; da[r] = s_da; ad[r] = s_ad; dd[r] = s_dd;
+  }
+}
+
+// one axis of the inverse for outputs k0 .. k0 + 3 (k0 = 4 q): inputs i = 2 q + e, e = 0 .. F/2; output k0 + o uses
+// taps j = (o & 1), +2, ... with e = (o + F - 2 - j) / 2; out-of-range inputs are loaded as 0 (the generic code skips them)
+template <int WAVE>
+__device__ __forceinline__ float idwt4(const float (&a)[WvCoef<WAVE>::F / 2 + 1], const float (&d)[WvCoef<WAVE>::F / 2 + 1], int o) {
+  using C = WvCoef<WAVE>;
+  float acc = 0.f;
+#pragma unroll
+  for (int j = 0; j < C::F; ++j) {
+    if ((j & 1) != (o & 1)) continue;
+    const int e = (o + C::F - 2 - j) / 2;
+    if (C::rec_lo(j) != 0.0f) acc = fmaf(C::rec_lo(j), a[e], acc);
+    if (C::rec_hi(j) != 0.0f) acc = fmaf(C::rec_hi(j), d[e], acc);
+  }
+  return acc;
+}
+
+template <int WAVE>
+__global__ void __launch_bounds__(256) k_idwt_rows_t(WvGeom g, float* ws, const WvStats* stats, int level) {
+  constexpr int NE = WvCoef<WAVE>::F / 2 + 1;
+  const int wl = g.w[level], wr = g.w[level - 1], y = blockIdx.y;
+  const int q = blockIdx.x * 256 + threadIdx.x, k0 = q * WV_RO;
+  if (k0 >= wr) return;
+  float* base = ws + (size_t)blockIdx.z * g.chan_floats;
+  const size_t r = (size_t)y * wl;
+  const float* app = base + g.off_app[level] + r;
+  const float* da = base + g.off_det[level][0] + r;
+  const float* ad = base + g.off_det[level][1] + r;
+  const float* dd = base + g.off_det[level][2] + r;
+  const float t_da = stats[blockIdx.z].thr[level][0], t_ad = stats[blockIdx.z].thr[level][1],
+              t_dd = stats[blockIdx.z].thr[level][2];
+  float va[NE], vad[NE], vda[NE], vdd[NE];
+#pragma unroll
+  for (int e = 0; e < NE; ++e) {
+    const int i = 2 * q + e;
+    const bool ok = i < wl;
+    va[e] = ok ? app[i] : 0.f;
+    vad[e] = ok ? wv_soft(ad[i], t_ad) : 0.f;
+    vda[e] = ok ? wv_soft(da[i], t_da) : 0.f;
+    vdd[e] = ok ? wv_soft(dd[i], t_dd) : 0.f;
+  }
+  float* lo = base + g.off_tlo + (size_t)y * wr;
+  float* hi = base + g.off_thi + (size_t)y * wr;
+#pragma unroll
+  for (int o = 0; o < WV_RO; ++o) {
+    if (k0 + o >= wr) break;
+    lo[k0 + o] = idwt4<WAVE>(va, vad, o);
+    hi[k0 + o] = idwt4<WAVE>(vda, vdd, o);
+  }
+}
+
+template <int WAVE>
+__global__ void __launch_bounds__(256) k_idwt_cols_t(WvGeom g, float* ws, int level) {
+  constexpr int NE = WvCoef<WAVE>::F / 2 + 1;
+  const int hl = g.h[level], wr = g.w[level - 1], hr = g.h[level - 1];
+  const int x = blockIdx.x * 256 + threadIdx.x, q = blockIdx.y, k0 = q * WV_RO;
+  if (x >= wr) return;
+  float* base = ws + (size_t)blockIdx.z * g.chan_floats;
+  const float* lo = base + g.off_tlo + x;
+  const float* hi = base + g.off_thi + x;
+  float vl[NE], vh[NE];
+#pragma unroll
+  for (int e = 0; e < NE; ++e) {
+    const int i = 2 * q + e;
+    const bool ok = i < hl;
+    vl[e] = ok ? lo[(size_t)i * wr] : 0.f;
+    vh[e] = ok ? hi[(size_t)i * wr] : 0.f;
+  }
+  float* out = base + (level == 1 ? g.off_plane : g.off_app[level - 1]) + x;
+#pragma unroll
+  for (int o = 0; o < WV_RO; ++o) {
+    if (k0 + o >= hr) break;
+    out[(size_t)(k0 + o) * wr] = idwt4<WAVE>(vl, vh, o);
   }
 }
 
@@ -537,17 +715,44 @@ int run_wavelet(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, int ki
       default: return fail(B2D_ERR_INVALID, "wavelet: bad noise operator %d", kind);
     }
     count_launch();
+    static const bool generic = [] { const char* e = getenv("B2D_WV_GENERIC"); return e && e[0] == '1'; }();
+    const bool db1 = sp.wavelet == B2D_WAVELET_DB1;
+    auto cdiv = [](int a, int b) { return (unsigned)((a + b - 1) / b); };
     for (int l = 1; l <= g.L; ++l) {
-      k_dwt_rows<<<dim3(blocks((size_t)g.h[l - 1] * g.w[l]), 1, planes), 256, 0, st>>>(
-          g, ws, l, l == 1 ? g.off_plane : g.off_app[l - 1]);
-      k_dwt_cols<<<dim3(blocks((size_t)g.h[l] * g.w[l]), 1, planes), 256, 0, st>>>(g, ws, l);
+      const size_t in_off = l == 1 ? g.off_plane : g.off_app[l - 1];
+      if (generic) {
+        k_dwt_rows<<<dim3(blocks((size_t)g.h[l - 1] * g.w[l]), 1, planes), 256, 0, st>>>(g, ws, l, in_off);
+        k_dwt_cols<<<dim3(blocks((size_t)g.h[l] * g.w[l]), 1, planes), 256, 0, st>>>(g, ws, l);
+      } else {
+        const dim3 gr(cdiv(cdiv(g.w[l], WV_RO), 256), (unsigned)g.h[l - 1], planes);
+        const dim3 gc(cdiv(g.w[l], 256), cdiv(g.h[l], WV_RO), planes);
+        if (db1) {
+          k_dwt_rows_t<B2D_WAVELET_DB1><<<gr, 256, 0, st>>>(g, ws, l, in_off);
+          k_dwt_cols_t<B2D_WAVELET_DB1><<<gc, 256, 0, st>>>(g, ws, l);
+        } else {
+          k_dwt_rows_t<B2D_WAVELET_BIOR15><<<gr, 256, 0, st>>>(g, ws, l, in_off);
+          k_dwt_cols_t<B2D_WAVELET_BIOR15><<<gc, 256, 0, st>>>(g, ws, l);
+        }
+      }
       k_band_energy<<<dim3(std::min(blocks((size_t)g.h[l] * g.w[l]), 64u), 1, planes), 256, 0, st>>>(g, ws, stats, l);
       count_launch(); count_launch(); count_launch();
     }
     wavelet_sigma_thresholds(g, ws, stats, hist, planes, st);
     for (int l = g.L; l >= 1; --l) {
-      k_idwt_rows<<<dim3(blocks((size_t)g.h[l] * g.w[l - 1]), 1, planes), 256, 0, st>>>(g, ws, stats, l);
-      k_idwt_cols<<<dim3(blocks((size_t)g.h[l - 1] * g.w[l - 1]), 1, planes), 256, 0, st>>>(g, ws, l);
+      if (generic) {
+        k_idwt_rows<<<dim3(blocks((size_t)g.h[l] * g.w[l - 1]), 1, planes), 256, 0, st>>>(g, ws, stats, l);
+        k_idwt_cols<<<dim3(blocks((size_t)g.h[l - 1] * g.w[l - 1]), 1, planes), 256, 0, st>>>(g, ws, l);
+      } else {
+        const dim3 gr(cdiv(cdiv(g.w[l - 1], WV_RO), 256), (unsigned)g.h[l], planes);
+        const dim3 gc(cdiv(g.w[l - 1], 256), cdiv(g.h[l - 1], WV_RO), planes);
+        if (db1) {
+          k_idwt_rows_t<B2D_WAVELET_DB1><<<gr, 256, 0, st>>>(g, ws, stats, l);
+          k_idwt_cols_t<B2D_WAVELET_DB1><<<gc, 256, 0, st>>>(g, ws, l);
+        } else {
+          k_idwt_rows_t<B2D_WAVELET_BIOR15><<<gr, 256, 0, st>>>(g, ws, stats, l);
+          k_idwt_cols_t<B2D_WAVELET_BIOR15><<<gc, 256, 0, st>>>(g, ws, l);
+        }
+      }
       count_launch(); count_launch();
     }
     k_wv_final<<<dim3(blocks(((size_t)p.h * p.w + 3) / 4), 1, cnt), 256, 0, st>>>(s, g, ws, stats, fa, first);

@@ -109,3 +109,34 @@ def test_haar_fast_path_equals_general_path(cuda, tmp_path):
     for key, a in outs["fast"].items():
         d = np.abs(a.astype(int) - outs["general"][key].astype(int))
         assert d.max() <= 1 and (d > 0).mean() < 2e-3, (key, d.max(), (d > 0).mean())
+
+
+def test_specialised_wavelet_kernels_equal_generic(cuda, tmp_path):
+    """The register-window kernels (compile-time taps, zero taps dropped, 4 outputs per thread) against
+    the generic per-output kernels (B2D_WV_GENERIC=1), bior1.5 and db1 / auto levels, odd sizes included:
+    same accumulation order, so the uint8 outputs must be identical."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = r"""
+import sys, numpy as np, torch
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[1] + "/tests")
+from conftest import synth_batch
+from image_denoising_b200 import api
+out = {}
+for h, w in ((37, 53), (120, 200), (375, 500), (601, 333)):
+    batch = torch.from_numpy(synth_batch(2, h, w, seed=41, kind="smooth")).cuda()
+    for spec, kw in (("gaussian_wavelet_var1.5", {}), ("original_wavelet", {}), ("sap_wavelet_var0.4", {"wavelet": "db1"}),
+                     ("speckle_wavelet_var1.0", {"wavelet": "db1", "levels": 2})):
+        out["%s%s@%dx%d" % (spec, sorted(kw.items()), h, w)] = api.apply(batch, spec, seed=11, **kw).cpu().numpy()
+np.savez(sys.argv[2], **out)
+"""
+    outs = {}
+    for tag, env in (("fast", {"B2D_HAAR": "0"}), ("generic", {"B2D_HAAR": "0", "B2D_WV_GENERIC": "1"})):
+        path = str(tmp_path / (tag + ".npz"))
+        subprocess.run([sys.executable, "-c", script, root, path], check=True, env=dict(os.environ, **env), timeout=600)
+        outs[tag] = dict(np.load(path))
+    assert set(outs["fast"]) == set(outs["generic"]) and len(outs["fast"]) == 16
+    for key, a in outs["fast"].items():
+        assert np.array_equal(a, outs["generic"][key]), (key, int((a != outs["generic"][key]).sum()))
