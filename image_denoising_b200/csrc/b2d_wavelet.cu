@@ -89,10 +89,17 @@ __global__ void __launch_bounds__(256) k_wv_color(ImageSet s, NoiseArgs na, WvGe
       const uint32_t grp = (uint32_t)(p8 * 3 + q);
       uint32_t v[8];
       float f[8];
+      const uint64_t e0 = (uint64_t)grp * 8;
+      if (e0 + 8 <= s.elems && (reinterpret_cast<uintptr_t>(img + e0) & 7u) == 0) {
+        const uint2 w8 = __ldg(reinterpret_cast<const uint2*>(img + e0));
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const uint64_t e = (uint64_t)grp * 8 + i;
-        v[i] = e < s.elems ? (uint32_t)__ldg(img + e) : 0u;
+        for (int i = 0; i < 4; ++i) {
+          v[i] = (w8.x >> (8 * i)) & 0xffu;
+          v[4 + i] = (w8.y >> (8 * i)) & 0xffu;
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = e0 + i < s.elems ? (uint32_t)__ldg(img + e0 + i) : 0u;
       }
       GroupCtx gc{(uint32_t)img_local, grp, img};
       apply8_float<KIND, MODE>(na, gc, v, f);
@@ -232,8 +239,16 @@ __global__ void __launch_bounds__(256) k_dwt_rows_t(WvGeom g, float* ws, int lev
   const int xlo = 2 * i0 + 2 - F;                              // x[2 i + 1 - j], j = 0 .. F-1, i = i0 .. i0 + 3
   float v[NIN];
   if (xlo >= 0 && xlo + NIN <= w) {
+    if (NIN % 4 == 0 && (reinterpret_cast<uintptr_t>(row + xlo) & 15u) == 0) {    // 16 floats as 4 x 16-byte loads
 #pragma unroll
-    for (int e = 0; e < NIN; ++e) v[e] = row[xlo + e];
+      for (int e = 0; e < NIN / 4; ++e) {
+        const float4 q = __ldg(reinterpret_cast<const float4*>(row + xlo) + e);
+        v[4 * e] = q.x; v[4 * e + 1] = q.y; v[4 * e + 2] = q.z; v[4 * e + 3] = q.w;
+      }
+    } else {
+#pragma unroll
+      for (int e = 0; e < NIN; ++e) v[e] = row[xlo + e];
+    }
   } else {
 #pragma unroll
     for (int e = 0; e < NIN; ++e) v[e] = row[sym_ext(xlo + e, w)];
