@@ -22,9 +22,22 @@ constexpr int MD_TILE_H = 16;
 constexpr int MD_APRON = 16;                       // >= 3 * 3 bytes, multiple of 4
 constexpr int MD_SROW = MD_TILE_WB + 2 * MD_APRON;
 
+// compare-exchange of two u16x2 words: VIMNMX.U16x2 min + max, ALU pipe, 2 cycles each: the networks saturate that
+// pipe (ncu: pipe_alu 93 %).  Tried: the maximum as HMNMX2 (`max.f16x2`; lanes 0x00vv are positive subnormal halves
+// ordered like the integers, results identical) hoping for the FMA pipe - ncu attributes HMNMX2 to the ALU pipe as
+// well and the kernel time does not move (10.10 ms either way), so the knob below stays off.
+#ifndef B2D_CE_HMAX
+#define B2D_CE_HMAX 0
+#endif
 __device__ __forceinline__ void ce(uint32_t& a, uint32_t& b) {
   const uint32_t lo = __vminu2(a, b);
+#if B2D_CE_HMAX
+  uint32_t hi;
+  asm("max.f16x2 %0, %1, %2;" : "=r"(hi) : "r"(a), "r"(b));
+  b = hi;
+#else
   b = __vmaxu2(a, b);
+#endif
   a = lo;
 }
 

@@ -1,6 +1,7 @@
 // pipes.cu - per-instruction issue cost on B200 (sm_100a): cycles per warp-instruction
 // per SM sub-partition at saturation.  Design input for the fused kernels.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o pipes pipes.cu ; run on the GPU box.
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -75,6 +76,14 @@ KERNEL(fmnmx, | 0x3f800000u, { float f = __uint_as_float(a[j]); f = fminf(f, __u
 KERNEL(fsel, | 0x3f800000u, { a[j] = (b & (1u << j)) ? a[j] + 1u : c; })
 KERNEL(shfl, , a[j] = __shfl_xor_sync(0xffffffffu, a[j], 1))
 
+// half2 min / max on the same 16-bit lanes as VIMNMX.U16x2 (bit patterns 0x00vv are positive subnormal halves, ordered
+// like the integers): which pipe, and do the two co-issue?
+KERNEL(hmnmx2, , { __half2 x = *reinterpret_cast<__half2*>(&a[j]); uint32_t bb = b & 0x00ff00ffu; __half2 y = *reinterpret_cast<__half2*>(&bb); x = __hmax2(x, y); a[j] = *reinterpret_cast<uint32_t*>(&x) + 1u; })
+KERNEL(hmnmx2_only, | 0x3c003c00u, { __half2 x = *reinterpret_cast<__half2*>(&a[j]); uint32_t bb = b & 0x00ff00ffu; __half2 y = *reinterpret_cast<__half2*>(&bb); x = __hmax2(x, y); a[j] = *reinterpret_cast<uint32_t*>(&x); })
+KERNEL(mix_vmin_hmax, , if (!(j & 1)) { uint32_t lo = __vminu2(a[j], a[j + 1]); __half2 x = *reinterpret_cast<__half2*>(&a[j]); __half2 y = *reinterpret_cast<__half2*>(&a[j + 1]); __half2 hi = __hmax2(x, y); a[j] = lo; a[j + 1] = *reinterpret_cast<uint32_t*>(&hi); })
+KERNEL(mix_vmin_hmax_indep, , if (j & 1) { a[j] = __vminu2(a[j], b) + 0u; } else { __half2 x = *reinterpret_cast<__half2*>(&a[j]); uint32_t bb = c & 0x00ff00ffu; __half2 y = *reinterpret_cast<__half2*>(&bb); x = __hmax2(x, y); a[j] = *reinterpret_cast<uint32_t*>(&x); })
+KERNEL(mix_vmin_vmax, , if (!(j & 1)) { uint32_t lo = __vminu2(a[j], a[j + 1]); uint32_t hi = __vmaxu2(a[j], a[j + 1]); a[j] = lo; a[j + 1] = hi; })
+
 // shared-memory read throughput
 template <int VEC>
 __global__ void __launch_bounds__(256) k_lds(uint32_t* out, uint32_t s, long long* cyc) {
@@ -119,6 +128,7 @@ int main() {
       E(mufu_ex2, full), E(mufu_rcp, full), E(i2f, full), E(i2f_u16, full), E(f2i, full), E(f2i_only, full),
       E(philox_round, full / 2), E(mix_prmt_imad, full), E(mix_lop_ffma, full), E(mix_mufu_alu, full),
       E(ffma2, full / 2), E(fadd2, full / 2), E(fmul2, full / 2), E(fmnmx, full), E(fsel, full), E(shfl, full),
+      E(hmnmx2, full), E(hmnmx2_only, full), E(mix_vmin_hmax, full), E(mix_vmin_hmax_indep, full), E(mix_vmin_vmax, full),
       {"lds32", k_lds<1>, 16.0}, {"lds64", k_lds<2>, 16.0}, {"lds128", k_lds<4>, 16.0},
   };
   printf("device %s, %d SMs, %d MHz max\n", p.name, nsm, p.clockRate / 1000);
