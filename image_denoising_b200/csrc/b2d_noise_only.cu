@@ -4,6 +4,8 @@
 // One thread per 8-element group, grid-stride; any image size / alignment.
 #include "b2d_kernels.cuh"
 
+#include <algorithm>
+
 namespace b2d {
 
 constexpr int NO_THREADS = 256;
@@ -63,8 +65,32 @@ __global__ void __launch_bounds__(NO_THREADS) k_noise_only(ImageSet s, NoiseArgs
   }
 }
 
+// generator mode on 16-byte aligned images: two groups per thread step, words never unpacked
+template <int KIND>
+__global__ void __launch_bounds__(NO_THREADS) k_noise_packed(ImageSet s, NoiseArgs na) {
+  const int img_local = image_of(s, blockIdx.z);
+  const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
+  const uint4* in = reinterpret_cast<const uint4*>(img);
+  uint4* out = reinterpret_cast<uint4*>(s.out + (uint64_t)img_local * s.elems);
+  const uint32_t chunks = (uint32_t)(s.elems >> 4);
+  for (uint32_t k = blockIdx.x * NO_THREADS + threadIdx.x; k < chunks; k += gridDim.x * NO_THREADS) {
+    const uint4 q = __ldg(in + k);
+    const uint2 a = PackedNoise<KIND>::apply(na, GroupCtx{(uint32_t)img_local, 2u * k, img}, make_uint2(q.x, q.y));
+    const uint2 b = PackedNoise<KIND>::apply(na, GroupCtx{(uint32_t)img_local, 2u * k + 1u, img}, make_uint2(q.z, q.w));
+    out[k] = make_uint4(a.x, a.y, b.x, b.y);
+  }
+}
+
 template <int KIND, int MODE>
 static cudaError_t launch_one(const ImageSet& s, const NoiseArgs& na, cudaStream_t st) {
+  if (MODE == NM_GEN && s.elems % 16 == 0 && s.out &&
+      ((reinterpret_cast<uintptr_t>(s.in) | reinterpret_cast<uintptr_t>(s.out)) & 15u) == 0) {
+    const uint32_t chunks = (uint32_t)(s.elems >> 4);
+    const uint32_t bx = std::min<uint32_t>((chunks + NO_THREADS - 1) / NO_THREADS, 148u * 8u);
+    k_noise_packed<KIND><<<dim3(bx, 1, s.count), NO_THREADS, 0, st>>>(s, na);
+    count_launch();
+    return cudaGetLastError();
+  }
   const uint32_t groups = (uint32_t)((s.elems + 7u) >> 3);
   uint32_t bx = (groups + NO_THREADS - 1) / NO_THREADS;
   if (bx > 148u * 8u) bx = 148u * 8u;             // grid-stride beyond 8 CTAs per SM
