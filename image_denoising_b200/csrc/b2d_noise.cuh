@@ -547,6 +547,35 @@ struct PackedNoise<NK_SHADER> {
   }
 };
 
+// uniform / rayleigh: x = v + 255 s >= 0, not clipped, ->u8 keeps the low byte of trunc(x) (wrap).  One
+// FFMA.RZ / FADD.RZ onto the magic number 2^23 + v leaves floor(x) in the mantissa: its low byte is the
+// result.  k + 0.5 comes from the 16-bit draw by PRMT + one exact FADD, as in normal_pair.
+template <bool RAYLEIGH>
+struct PackedAdditive {
+  static constexpr bool kNative = true;
+  template <int I>
+  static __device__ __forceinline__ uint32_t elem(uint32_t w, float kf, float c) {
+    const float mv = magic_byte<I>(w);
+    if (RAYLEIGH) {                                               // 255 * scale * sqrt(-2 ln((k + 0.5) / 65536))
+      const float rad = fast_sqrt(fmaf(fast_lg2(kf), -c, 16.0f * c));
+      return __float_as_uint(__fadd_rz(rad, mv));
+    }
+    return __float_as_uint(__fmaf_rz(kf, c, mv));                 // 255 * high * (k + 0.5) / 65536
+  }
+  static __device__ __forceinline__ uint2 apply(const NoiseArgs& a, const GroupCtx& g, uint2 w) {
+    const uint4 r = group_random(a, g, 0);
+    const float c = RAYLEIGH ? 1.3862943611198906f * (255.0f * a.p0) * (255.0f * a.p0) : a.p0 * (255.0f / 65536.0f);
+    const uint32_t t0 = elem<0>(w.x, magic_lo16(r.x) - 8388607.5f, c), t1 = elem<1>(w.x, magic_hi16(r.x) - 8388607.5f, c);
+    const uint32_t t2 = elem<2>(w.x, magic_lo16(r.y) - 8388607.5f, c), t3 = elem<3>(w.x, magic_hi16(r.y) - 8388607.5f, c);
+    const uint32_t t4 = elem<0>(w.y, magic_lo16(r.z) - 8388607.5f, c), t5 = elem<1>(w.y, magic_hi16(r.z) - 8388607.5f, c);
+    const uint32_t t6 = elem<2>(w.y, magic_lo16(r.w) - 8388607.5f, c), t7 = elem<3>(w.y, magic_hi16(r.w) - 8388607.5f, c);
+    return make_uint2(prmt(prmt(t0, t1, 0x0040u), prmt(t2, t3, 0x0040u), 0x5410u),
+                      prmt(prmt(t4, t5, 0x0040u), prmt(t6, t7, 0x0040u), 0x5410u));
+  }
+};
+template <> struct PackedNoise<NK_UNIFORM> : PackedAdditive<false> {};
+template <> struct PackedNoise<NK_RAYLEIGH> : PackedAdditive<true> {};
+
 template <> struct PackedNoise<NK_GAUSSIAN> : PackedNormal<false> {};
 template <> struct PackedNoise<NK_SPECKLE> : PackedNormal<true> {};
 
