@@ -42,7 +42,7 @@ class B2DError(RuntimeError):
 
 EXPORTS = ["b2d_parse_spec", "b2d_plan_create", "b2d_plan_workspace_bytes", "b2d_plan_destroy", "b2d_run",
            "b2d_run_host", "b2d_host_register", "b2d_host_unregister", "b2d_noise_field", "b2d_stats", "b2d_lab_convert",
-           "b2d_poisson_table", "b2d_blob_shape", "b2d_blob_prep", "b2d_launch_count", "b2d_reset_launch_count", "b2d_last_error", "b2d_version"]
+           "b2d_poisson_table", "b2d_gamma_table", "b2d_blob_shape", "b2d_blob_prep", "b2d_launch_count", "b2d_reset_launch_count", "b2d_last_error", "b2d_version"]
 
 _lib = None
 
@@ -82,6 +82,7 @@ def lib():
     L.b2d_stats.argtypes = [vp, vp, vp, vp, vp, vp]
     L.b2d_lab_convert.argtypes = [vp, vp, sz, ctypes.c_int, vp]
     L.b2d_poisson_table.argtypes = [ctypes.c_int, vp]
+    L.b2d_gamma_table.argtypes = [ctypes.c_double, vp, vp, vp]
     L.b2d_blob_shape.argtypes = [ctypes.c_int] * 4 + [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int),
                                                       ctypes.POINTER(ctypes.c_int)]
     L.b2d_blob_prep.argtypes = [vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, ctypes.c_int, ctypes.c_int,
@@ -92,7 +93,7 @@ def lib():
     L.b2d_version.restype = ctypes.c_char_p
     for name in ("b2d_parse_spec", "b2d_plan_create", "b2d_plan_workspace_bytes", "b2d_run", "b2d_run_host",
                  "b2d_host_register", "b2d_host_unregister", "b2d_noise_field", "b2d_stats", "b2d_lab_convert",
-                 "b2d_poisson_table", "b2d_blob_shape", "b2d_blob_prep"):
+                 "b2d_poisson_table", "b2d_gamma_table", "b2d_blob_shape", "b2d_blob_prep"):
         getattr(L, name).restype = ctypes.c_int
     _lib = L
     return L

@@ -89,7 +89,11 @@ int run_group(const RunCtx& c, const SpecGroup& g, int lo, int hi) {
       break;
     case B2D_NOISE_UNIFORM: kind = NK_UNIFORM; na.p0 = (float)sp.level; break;
     case B2D_NOISE_RAYLEIGH: kind = NK_RAYLEIGH; na.p0 = (float)sp.level; break;
-    case B2D_NOISE_GAMMA: kind = NK_GAMMA; na.p0 = (float)sp.level; break;
+    case B2D_NOISE_GAMMA:
+      kind = NK_GAMMA; na.p0 = (float)sp.level;
+      for (const GammaTable& t : p->gamma)
+        if (t.level == sp.level) { na.tab = t.d_tab; na.u0 = (uint32_t)t.folds; }
+      break;
     case B2D_NOISE_SHADER: kind = NK_SHADER; na.u0 = (sp.compat_flags & B2D_COMPAT_SHADER_BGR) ? 1u : 0u; break;
     case B2D_NOISE_POISSON: {
       kind = NK_POISSON;
@@ -265,7 +269,11 @@ extern "C" int b2d_noise_field(b2d_plan* plan, float* d_f0, float* d_f1, uint64_
         break;
       case B2D_NOISE_UNIFORM: kind = NK_UNIFORM; na.p0 = (float)sp.level; break;
       case B2D_NOISE_RAYLEIGH: kind = NK_RAYLEIGH; na.p0 = (float)sp.level; break;
-      case B2D_NOISE_GAMMA: kind = NK_GAMMA; na.p0 = (float)sp.level; break;
+      case B2D_NOISE_GAMMA:
+        kind = NK_GAMMA; na.p0 = (float)sp.level;
+        for (const GammaTable& t : plan->gamma)
+          if (t.level == sp.level) { na.tab = t.d_tab; na.u0 = (uint32_t)t.folds; }
+        break;
       default: return fail(B2D_ERR_UNSUPPORTED, "b2d_noise_field: noise %d has no dumpable field", sp.noise);
     }
     // the operators never read pixels in dump mode except poisson (not dumpable): `in` may be any valid buffer

@@ -222,7 +222,34 @@ struct NoiseOp<NK_RAYLEIGH, MODE> {
   }
 };
 
-// Marsaglia-Tsang for shape a = 1.99 (d = a - 1/3, c = 1/sqrt(9 d)).  Each
+// Test hook (NM_DUMP) of the table sampler: unfold K = R + 256 h with h drawn from the plan's fold
+// table (substream 1), place the sample inside [K, K + 1) by inverting a linear density through the
+// gamma pdf at both ends (substream 2; K = 0: cdf ~ x^1.99), and write (K + u) / 255.
+static __device__ __noinline__ void gamma_dump8(const NoiseArgs& a, const GroupCtx& g, const uint32_t (&k)[8]) {
+  const uint32_t folds = a.u0;
+  const uint32_t* fold = reinterpret_cast<const uint32_t*>(a.tab + 512);
+  const uint4 rh = group_random(a, g, 1), rj = group_random(a, g, 2);
+  const float q1 = __expf(-1.0f / (255.0f * a.p0));
+  for (int i = 0; i < 8; ++i) {
+    if (!in_image(a, g, i)) continue;
+    const uint32_t uh = r16(rh, i);
+    uint32_t h = 0;
+    while (h + 1 < folds && uh >= fold[k[i] * folds + h]) ++h;
+    const float K = (float)(k[i] + 256u * h);
+    const float U = ((float)r16(rj, i) + 0.5f) * (1.0f / 65536.0f);
+    float u;
+    if (K == 0.0f) {
+      u = exp2f(log2f(U) * (1.0f / 1.99f));
+    } else {
+      const float q = powf((K + 1.0f) / K, 0.99f) * q1, dq = q - 1.0f;
+      u = fabsf(dq) < 1e-3f ? U : (sqrtf(fmaf(q * q - 1.0f, U, 1.0f)) - 1.0f) / dq;
+    }
+    u = fminf(fmaxf(u, 0.004f), 0.996f);
+    a.dump0[field_index(a, g, i)] = (K + u) / 255.0f;
+  }
+}
+
+// Float view: Marsaglia-Tsang for shape a = 1.99 (d = a - 1/3, c = 1/sqrt(9 d)).  Each
 // attempt t draws one Philox block per 4 elements (substream 2t + half):
 // words 0,1 -> 4 normals, words 2,3 -> 4 acceptance uniforms.
 template <int MODE>
@@ -235,6 +262,24 @@ struct NoiseOp<NK_GAMMA, MODE> {
         if (in_image(a, g, i)) v[i] = add_wrap_inject(v[i], a.f0[field_index(a, g, i)], xf ? xf + i : nullptr);
       return;
     }
+    if (xf == nullptr) {
+      // uint8 consumers: out = (v + K) mod 256 with K = floor(255 * scale * G); R = K mod 256 comes from
+      // the plan's alias table (b2d_gamma.cu), low byte of the 16 random bits = slot, high byte = u
+      const uint16_t* tab = reinterpret_cast<const uint16_t*>(a.tab);
+      const uint4 r = group_random(a, g, 0);
+      uint32_t k[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const uint32_t rr = r16(r, i);
+        const uint32_t e = __ldg(tab + (rr & 0xffu));
+        k[i] = (rr < (e & 0xff00u) ? rr : e) & 0xffu;
+      }
+      if (MODE == NM_DUMP) gamma_dump8(a, g, k);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = (v[i] + k[i]) & 0xffu;
+      return;
+    }
+    // float view (wavelet consumers): Marsaglia-Tsang samples
     const float d = 1.99f - 1.0f / 3.0f;
     const float c = 0.25897428f;  // 1 / sqrt(9 d)
     float smp[8];
@@ -573,6 +618,28 @@ struct PackedAdditive {
                       prmt(prmt(t4, t5, 0x0040u), prmt(t6, t7, 0x0040u), 0x5410u));
   }
 };
+// gamma: R = K mod 256 of eight elements from the alias table, one wrapping byte add per word
+template <>
+struct PackedNoise<NK_GAMMA> {
+  static constexpr bool kNative = true;
+  static __device__ __forceinline__ uint2 apply(const NoiseArgs& a, const GroupCtx& g, uint2 w) {
+    const uint16_t* tab = reinterpret_cast<const uint16_t*>(a.tab);
+    const uint4 r = group_random(a, g, 0);
+    const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
+    uint32_t o[8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t r0 = rw[j] & 0xffffu, r1 = rw[j] >> 16;
+      const uint32_t e0 = __ldg(tab + (r0 & 0xffu)), e1 = __ldg(tab + (r1 & 0xffu));
+      o[2 * j] = r0 < (e0 & 0xff00u) ? r0 : e0;                                  // low byte = R
+      o[2 * j + 1] = r1 < (e1 & 0xff00u) ? r1 : e1;
+    }
+    const uint32_t kx = prmt(prmt(o[0], o[1], 0x0040u), prmt(o[2], o[3], 0x0040u), 0x5410u);
+    const uint32_t ky = prmt(prmt(o[4], o[5], 0x0040u), prmt(o[6], o[7], 0x0040u), 0x5410u);
+    return make_uint2(__vadd4(w.x, kx), __vadd4(w.y, ky));
+  }
+};
+
 template <> struct PackedNoise<NK_UNIFORM> : PackedAdditive<false> {};
 template <> struct PackedNoise<NK_RAYLEIGH> : PackedAdditive<true> {};
 

@@ -22,6 +22,12 @@ struct PeriodicTable {
   uint8_t* d_tab;            // elems bytes
 };
 
+struct GammaTable {
+  double level;              // scale
+  uint8_t* d_tab;            // 512-byte alias table + fold table (b2d_gamma.cu)
+  int folds;
+};
+
 }  // namespace b2d
 
 struct b2d_plan {
@@ -29,6 +35,7 @@ struct b2d_plan {
   uint64_t elems;
   std::vector<b2d::SpecGroup> groups;
   std::vector<b2d::PeriodicTable> periodic;
+  std::vector<b2d::GammaTable> gamma;
   uint8_t* d_poisson;        // alias tables of the Poisson generator (b2d_poisson.cu), when a group needs them
   // workspace layout (byte offsets into the caller's d_ws)
   size_t ws_bytes, off_par, off_bitmap, off_stage, off_aux, off_scan, off_denoise, off_pix;

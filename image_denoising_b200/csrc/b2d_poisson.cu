@@ -29,26 +29,11 @@ constexpr int PO_THREADS = 1024;
 
 size_t poisson_tables_bytes() { return PO_TABLES * PO_TABLE_BYTES; }
 
-// host: distribution of the output byte for input value v -> integer weights (sum 65536) -> alias row
-static void build_row(int t, int v, uint16_t* row) {
-  const int vals = 1 << t;
-  const double lam = (double)v / 255.0 * (double)vals;                // img_as_float(image) * vals
-  double P[PO_SLOTS] = {0.0};
-  if (lam <= 0.0) {
-    P[0] = 1.0;
-  } else {
-    double total = 0.0;
-    const double ll = std::log(lam);
-    for (int k = 0; k < vals; ++k) {
-      const double p = std::exp(-lam + k * ll - std::lgamma((double)k + 1.0));
-      P[(255 * k) >> t] += p;
-      total += p;
-    }
-    P[255] += std::fmax(0.0, 1.0 - total);                            // k >= vals clips to 1.0 -> 255
-  }
+// host: 256 probabilities -> integer weights (sum 65536, largest remainders) -> alias row.
+// Vose on integers: every slot ends with exactly 256 units, thr of its own outcome + the rest of its alias.
+void alias_row_256(const double* P, uint16_t* row) {
   double sum = 0.0;
   for (int i = 0; i < PO_SLOTS; ++i) sum += P[i];
-  // largest-remainder rounding to units of 2^-16
   int w[PO_SLOTS], order[PO_SLOTS], units = 0;
   double frac[PO_SLOTS];
   for (int i = 0; i < PO_SLOTS; ++i) {
@@ -60,7 +45,6 @@ static void build_row(int t, int v, uint16_t* row) {
   }
   std::sort(order, order + PO_SLOTS, [&](int a, int b) { return frac[a] > frac[b] || (frac[a] == frac[b] && a < b); });
   for (int j = 0; units < 65536; ++j, ++units) ++w[order[j % PO_SLOTS]];
-  // Vose on integers: every slot ends with exactly 256 units, thr of its own outcome + the rest of its alias
   int thr[PO_SLOTS], alias[PO_SLOTS], small[PO_SLOTS], large[PO_SLOTS], ns = 0, nl = 0;
   for (int i = 0; i < PO_SLOTS; ++i) {
     thr[i] = 256;
@@ -79,6 +63,26 @@ static void build_row(int t, int v, uint16_t* row) {
     const int th = thr[i] >= 256 ? 255 : thr[i], al = thr[i] >= 256 ? i : alias[i];
     row[i] = (uint16_t)(al | (th << 8));
   }
+}
+
+// distribution of the output byte for input value v
+static void build_row(int t, int v, uint16_t* row) {
+  const int vals = 1 << t;
+  const double lam = (double)v / 255.0 * (double)vals;                // img_as_float(image) * vals
+  double P[PO_SLOTS] = {0.0};
+  if (lam <= 0.0) {
+    P[0] = 1.0;
+  } else {
+    double total = 0.0;
+    const double ll = std::log(lam);
+    for (int k = 0; k < vals; ++k) {
+      const double p = std::exp(-lam + k * ll - std::lgamma((double)k + 1.0));
+      P[(255 * k) >> t] += p;
+      total += p;
+    }
+    P[255] += std::fmax(0.0, 1.0 - total);                            // k >= vals clips to 1.0 -> 255
+  }
+  alias_row_256(P, row);
 }
 
 void poisson_table_host(int t, uint16_t* tab) {

@@ -14,6 +14,11 @@ struct BrownianArgs {
 uint32_t brownian_chunks(uint64_t elems);
 // generator-mode Poisson through per-`vals` alias tables (b2d_poisson.cu); img_par = vals per image
 cudaError_t upload_poisson_tables(uint8_t** d_tables);
+// 256 probabilities -> alias row (alias | threshold << 8), probabilities rounded to 2^-16
+void alias_row_256(const double* P, uint16_t* row);
+// generator-mode gamma: alias table over K mod 256 + fold table for the test hook (b2d_gamma.cu)
+int gamma_folds(double scale);
+cudaError_t upload_gamma_table(double scale, uint8_t** d_table);
 cudaError_t launch_poisson(const ImageSet& s, const NoiseArgs& na, const uint8_t* tables, cudaStream_t st);
 cudaError_t launch_poisson_vals(const ImageSet& s, uint32_t* bitmaps, float* vals, int n_batch, cudaStream_t st);
 cudaError_t launch_periodic_table(uint8_t* tab, uint64_t n, double lim, cudaStream_t st);

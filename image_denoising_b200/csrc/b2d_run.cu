@@ -31,6 +31,8 @@ static int validate_spec(const b2d_spec& s, int h, int w) {
     return fail(B2D_ERR_INVALID, "bloom needs H >= 300 (randint(1, H//100-2), Automold.py:583)");
   if (s.noise == B2D_NOISE_QUANT && (s.level < 1 || s.level > 32))
     return fail(B2D_ERR_INVALID, "quant k must be in [1, 32]");
+  if (s.noise == B2D_NOISE_GAMMA && !(s.level > 0.0 && s.level <= 100.0))
+    return fail(B2D_ERR_INVALID, "gamma scale %g outside (0, 100]", s.level);
   if ((s.noise == B2D_NOISE_GAUSSIAN || s.noise == B2D_NOISE_SPECKLE) && !(s.level >= 0.0 && s.level <= 100.0))
     return fail(B2D_ERR_INVALID, "gaussian / speckle var must be in [0, 100] (packed generator range)");
   (void)w;
@@ -90,6 +92,20 @@ extern "C" int b2d_plan_create(b2d_plan** out, int device, int n, int h, int w, 
         return fail_cuda(e, "poisson tables");
       }
     }
+    if (nz == B2D_NOISE_GAMMA) {
+      bool have = false;
+      for (const GammaTable& t : p->gamma) have = have || t.level == g.spec.level;
+      if (!have) {
+        GammaTable t{g.spec.level, nullptr, gamma_folds(g.spec.level)};
+        const cudaError_t e = upload_gamma_table(g.spec.level, &t.d_tab);
+        if (e != cudaSuccess) {
+          if (t.d_tab) cudaFree(t.d_tab);
+          b2d_plan_destroy(p);
+          return fail_cuda(e, "gamma table");
+        }
+        p->gamma.push_back(t);
+      }
+    }
     if (nz == B2D_NOISE_PERIODIC) {
       bool have = false;
       for (const PeriodicTable& t : p->periodic) have = have || t.level == g.spec.level;
@@ -144,6 +160,8 @@ extern "C" void b2d_plan_destroy(b2d_plan* p) {
   for (SpecGroup& g : p->groups)
     if (g.d_list) cudaFree(g.d_list);
   for (PeriodicTable& t : p->periodic)
+    if (t.d_tab) cudaFree(t.d_tab);
+  for (GammaTable& t : p->gamma)
     if (t.d_tab) cudaFree(t.d_tab);
   if (p->d_poisson) cudaFree(p->d_poisson);
   if (p->h_d_in) cudaFree(p->h_d_in);

@@ -159,6 +159,15 @@ int b2d_lab_convert(const uint8_t* d_in, uint8_t* d_out, size_t n_pixels, int di
  * value, otherwise the alias is the output byte). */
 int b2d_poisson_table(int log2_vals, uint16_t* h_table);
 
+/* Test hook (host only, no GPU needed): the tables of the generator-mode gamma corruption
+ * (scipy.stats.gamma.rvs(1.99, scale) added with cv2.add and cast with wrap-around,
+ * lib/roi_data_layer/minibatch.py:1216-1217,1247; twin lib/model/test.py).  With
+ * K = floor(255 * scale * G) the uint8 result is (v + K) mod 256; h_alias[256] is the alias table
+ * (alias | threshold << 8, as above) over R = K mod 256.  If h_fold is non-null it receives
+ * h_fold[R * folds + j] = round(65536 * P(K <= R + 256 j | K mod 256 = R)), which b2d_noise_field uses
+ * to unfold K; *folds (at most 64) is written when `folds` is non-null, so h_fold needs 256 * 64 entries. */
+int b2d_gamma_table(double scale, uint16_t* h_alias, uint32_t* h_fold, int* folds);
+
 /* ---- next stage: the network input blob, on the device ------------------------
  * b2d_blob_shape: geometry of prep_im_for_blob (lib/utils/blob.py:37-45) for an h x w image:
  *   im_scale = target_size / min(h, w), capped so that round(im_scale * max(h, w)) <= max_size;

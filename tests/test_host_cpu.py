@@ -138,6 +138,39 @@ def test_poisson_alias_table_represents_the_pmf(log2_vals):
         _lib.check(L.b2d_poisson_table(9, tab.ctypes.data_as(ctypes.c_void_p)))
 
 
+@pytest.mark.parametrize("scale", [0.05, 0.1, 0.2, 0.7])
+def test_gamma_alias_table_represents_the_folded_pmf(scale):
+    """b2d_gamma_table (host code of the library): the alias table must reproduce the pmf of
+    floor(255 * gamma.rvs(1.99, scale=S)) mod 256 (minibatch.py:1216-1217,1247: unclipped cv2.add,
+    wrapping ->u8) to 2^-16 per outcome, and the fold table the conditional cdf of K // 256."""
+    import ctypes
+    from scipy.stats import gamma
+    L = _lib.lib()
+    alias_tab = np.zeros(256, np.uint16)
+    fold = np.zeros(256 * 64, np.uint32)
+    folds = ctypes.c_int(0)
+    _lib.check(L.b2d_gamma_table(scale, alias_tab.ctypes.data_as(ctypes.c_void_p), fold.ctypes.data_as(ctypes.c_void_p),
+                                 ctypes.byref(folds)))
+    nf = folds.value
+    assert 1 <= nf <= 64 and 256 * nf >= min(255 * scale * 40, 256 * 64 - 1)
+    edges = np.arange(256 * nf + 1) / (255.0 * scale)
+    cdf = gamma(1.99, scale=1.0).cdf(edges)
+    cdf[-1] = 1.0
+    pk = np.diff(cdf).reshape(nf, 256)
+    want = pk.sum(axis=0)
+    alias, thr = (alias_tab & 0xff).astype(np.int64), (alias_tab >> 8).astype(np.int64)
+    own = np.where(alias == np.arange(256), 256, thr)
+    got = np.bincount(np.arange(256), weights=own, minlength=256) + np.bincount(alias, weights=256 - own, minlength=256)
+    assert got.sum() == 65536
+    assert np.abs(got / 65536.0 - want).max() <= 1.0 / 65536 + 1e-10, scale
+    f = fold[:256 * nf].reshape(256, nf).astype(np.float64) / 65536.0
+    cond = np.cumsum(pk, axis=0).T / np.maximum(want, 1e-300)[:, None]
+    assert np.abs(f - cond).max() <= 0.5 / 65536 + 1e-9
+    assert np.all(f[:, -1] == 1.0)
+    with pytest.raises(_lib.B2DError):
+        _lib.check(L.b2d_gamma_table(0.0, alias_tab.ctypes.data_as(ctypes.c_void_p), None, None))
+
+
 def test_blob_shape_matches_host_mirror():
     """b2d_blob_shape (host code of the library) == the scale / dsize of the reference's
     prep_im_for_blob through cv2.resize (lib/utils/blob.py:37-45), over many image sizes."""
