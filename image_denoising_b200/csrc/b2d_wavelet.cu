@@ -106,17 +106,39 @@ __global__ void __launch_bounds__(256) k_wv_color(ImageSet s, NoiseArgs na, WvGe
 #pragma unroll
       for (int i = 0; i < 8; ++i) xf[8 * q + i] = f[i] * (1.0f / 255.0f);
     }
+    // a thread owns 8 consecutive pixels: colour transform in registers, then two 16-byte stores per
+    // plane (scalar stores touched 24 x 32 sectors per warp step and ran at 1.2 TB/s)
+    float yv[3][8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      const uint64_t pix = p8 * 8 + k;
-      if (pix >= npix) break;
       const float c0 = xf[3 * k], c1 = xf[3 * k + 1], c2 = xf[3 * k + 2];
 #pragma unroll
+      for (int c = 0; c < 3; ++c)
+        yv[c][k] = kYCC[c][0] * c0 + kYCC[c][1] * c1 + kYCC[c][2] * c2 + (c == 0 ? 16.0f : 128.0f);
+    }
+    const uint64_t pix0 = p8 * 8;
+    if (pix0 + 8 <= npix && (reinterpret_cast<uintptr_t>(base + g.off_plane) & 15u) == 0) {
+#pragma unroll
       for (int c = 0; c < 3; ++c) {
-        const float y = kYCC[c][0] * c0 + kYCC[c][1] * c1 + kYCC[c][2] * c2 + (c == 0 ? 16.0f : 128.0f);
-        base[(size_t)c * g.chan_floats + g.off_plane + pix] = y;
-        mn[c] = fminf(mn[c], y);
-        mx[c] = fmaxf(mx[c], y);
+        float4* dst = reinterpret_cast<float4*>(base + (size_t)c * g.chan_floats + g.off_plane + pix0);
+        dst[0] = make_float4(yv[c][0], yv[c][1], yv[c][2], yv[c][3]);
+        dst[1] = make_float4(yv[c][4], yv[c][5], yv[c][6], yv[c][7]);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          mn[c] = fminf(mn[c], yv[c][k]);
+          mx[c] = fmaxf(mx[c], yv[c][k]);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (pix0 + k >= npix) break;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          base[(size_t)c * g.chan_floats + g.off_plane + pix0 + k] = yv[c][k];
+          mn[c] = fminf(mn[c], yv[c][k]);
+          mx[c] = fmaxf(mx[c], yv[c][k]);
+        }
       }
     }
   }
@@ -380,6 +402,180 @@ __global__ void __launch_bounds__(256) k_idwt_cols_t(WvGeom g, float* ws, int le
   for (int o = 0; o < WV_RO; ++o) {
     if (k0 + o >= hr) break;
     out[(size_t)(k0 + o) * wr] = idwt4<WAVE>(vl, vh, o);
+  }
+}
+
+// ---- fused 2-D versions (the ones that run): rows and columns of one level in ONE kernel, the row
+// pass result lives in shared memory instead of the tlo / thi planes (a level cost read 1 + write 1 +
+// read 1 + write 1 planes + a read of the three detail bands for their energies; now read 1 + write 1).
+// Arithmetic, operand order and rounding are those of k_dwt_rows_t / k_dwt_cols_t / k_idwt_rows_t /
+// k_idwt_cols_t above (B2D_WV_FUSED=0 runs those; tests/test_gpu_wavelet.py compares the two paths).
+constexpr int WV_FOY = 16, WV_FOX = 64;                        // forward: coefficient tile per CTA
+constexpr int WV_IY = 32, WV_IX = 128;                         // inverse: output tile per CTA
+
+template <int WAVE>
+__global__ void __launch_bounds__(256) k_dwt2_t(WvGeom g, float* ws, WvStats* stats, int level, size_t in_off) {
+  using C = WvCoef<WAVE>;
+  constexpr int F = C::F, NIN = F + 2 * (WV_RO - 1), RIN = 2 * WV_FOY + F - 2;
+  __shared__ __align__(16) float s_lo[RIN][WV_FOX];
+  __shared__ __align__(16) float s_hi[RIN][WV_FOX];
+  __shared__ double s_e[8][3];
+  const int h = g.h[level - 1], w = g.w[level - 1], ho = g.h[level], wo = g.w[level];
+  const int ox0 = blockIdx.x * WV_FOX, oy0 = blockIdx.y * WV_FOY;
+  float* base = ws + (size_t)blockIdx.z * g.chan_floats;
+  const float* in = base + in_off;
+  const int nout_y = min(WV_FOY, ho - oy0);
+  const int rows = 2 * nout_y + F - 2;                         // input rows 2 oy0 + 2 - F ... of this tile
+  const int ylo = 2 * oy0 + 2 - F;
+  // 1. along x into shared memory: item = (input row, group of 4 coefficients)
+  for (int item = threadIdx.x; item < rows * (WV_FOX / WV_RO); item += 256) {
+    const int r = item / (WV_FOX / WV_RO), q = item - r * (WV_FOX / WV_RO);
+    const int i0 = ox0 + q * WV_RO;
+    if (i0 >= wo) continue;
+    const float* row = in + (size_t)sym_ext(ylo + r, h) * w;
+    const int xlo = 2 * i0 + 2 - F;
+    float v[NIN];
+    if (xlo >= 0 && xlo + NIN <= w) {
+      if (NIN % 4 == 0 && (reinterpret_cast<uintptr_t>(row + xlo) & 15u) == 0) {
+#pragma unroll
+        for (int e = 0; e < NIN / 4; ++e) {
+          const float4 t4 = __ldg(reinterpret_cast<const float4*>(row + xlo) + e);
+          v[4 * e] = t4.x; v[4 * e + 1] = t4.y; v[4 * e + 2] = t4.z; v[4 * e + 3] = t4.w;
+        }
+      } else {
+#pragma unroll
+        for (int e = 0; e < NIN; ++e) v[e] = row[xlo + e];
+      }
+    } else {
+#pragma unroll
+      for (int e = 0; e < NIN; ++e) v[e] = row[sym_ext(xlo + e, w)];
+    }
+    float a[WV_RO], d[WV_RO];
+#pragma unroll
+    for (int o = 0; o < WV_RO; ++o) {
+      a[o] = 0.f; d[o] = 0.f;
+#pragma unroll
+      for (int j = 0; j < F; ++j) {
+        const float x = v[2 * o + F - 1 - j];
+        if (C::dec_lo(j) != 0.0f) a[o] = __fadd_rn(a[o], __fmul_rn(C::dec_lo(j), x));
+        if (C::dec_hi(j) != 0.0f) d[o] = __fadd_rn(d[o], __fmul_rn(C::dec_hi(j), x));
+      }
+    }
+    *reinterpret_cast<float4*>(&s_lo[r][q * WV_RO]) = make_float4(a[0], a[1], a[2], a[3]);
+    *reinterpret_cast<float4*>(&s_hi[r][q * WV_RO]) = make_float4(d[0], d[1], d[2], d[3]);
+  }
+  __syncthreads();
+  // 2. along y out of shared memory: thread = (column, group of 4 coefficient rows)
+  const int xl = threadIdx.x % WV_FOX, grp = threadIdx.x / WV_FOX, x = ox0 + xl;
+  double e_da = 0.0, e_ad = 0.0, e_dd = 0.0;
+  if (x < wo && grp * WV_RO < nout_y) {
+    float vl[NIN], vh[NIN];
+#pragma unroll
+    for (int e = 0; e < NIN; ++e) {
+      const int r = min(2 * grp * WV_RO + e, rows - 1);        // rows past the tile's last output are never used
+      vl[e] = s_lo[r][xl];
+      vh[e] = s_hi[r][xl];
+    }
+    float* aa = base + g.off_app[level] + x;
+    float* da = base + g.off_det[level][0] + x;
+    float* ad = base + g.off_det[level][1] + x;
+    float* dd = base + g.off_det[level][2] + x;
+#pragma unroll
+    for (int o = 0; o < WV_RO; ++o) {
+      const int i = oy0 + grp * WV_RO + o;
+      if (i >= ho) break;
+      float s_aa = 0.f, s_da = 0.f, s_ad = 0.f, s_dd = 0.f;
+#pragma unroll
+      for (int j = 0; j < F; ++j) {
+        const float l = vl[2 * o + F - 1 - j], hv = vh[2 * o + F - 1 - j];
+        if (C::dec_lo(j) != 0.0f) { s_aa = __fadd_rn(s_aa, __fmul_rn(C::dec_lo(j), l)); s_ad = __fadd_rn(s_ad, __fmul_rn(C::dec_lo(j), hv)); }
+        if (C::dec_hi(j) != 0.0f) { s_da = __fadd_rn(s_da, __fmul_rn(C::dec_hi(j), l)); s_dd = __fadd_rn(s_dd, __fmul_rn(C::dec_hi(j), hv)); }
+      }
+      const size_t r = (size_t)i * wo;
+      aa[r] = s_aa; da[r] = s_da; ad[r] = s_ad; dd[r] = s_dd;
+      e_da += (double)s_da * s_da;
+      e_ad += (double)s_ad * s_ad;
+      e_dd += (double)s_dd * s_dd;
+    }
+  }
+  // band energies (k_band_energy's sums, taken while the coefficients are in registers)
+  for (int o = 16; o; o >>= 1) {
+    e_da += __shfl_xor_sync(0xffffffffu, e_da, o);
+    e_ad += __shfl_xor_sync(0xffffffffu, e_ad, o);
+    e_dd += __shfl_xor_sync(0xffffffffu, e_dd, o);
+  }
+  if ((threadIdx.x & 31) == 0) { s_e[threadIdx.x >> 5][0] = e_da; s_e[threadIdx.x >> 5][1] = e_ad; s_e[threadIdx.x >> 5][2] = e_dd; }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    double t = 0.0;
+    for (int k = 0; k < 8; ++k) t += s_e[k][threadIdx.x];
+    atomicAdd(&stats[blockIdx.z].energy[level][threadIdx.x], t);
+  }
+}
+
+template <int WAVE>
+__global__ void __launch_bounds__(256) k_idwt2_t(WvGeom g, float* ws, const WvStats* stats, int level) {
+  constexpr int NE = WvCoef<WAVE>::F / 2 + 1, RC = WV_IY / 2 + NE - 2;
+  __shared__ __align__(16) float s_lo[RC][WV_IX];
+  __shared__ __align__(16) float s_hi[RC][WV_IX];
+  const int hl = g.h[level], wl = g.w[level], hr = g.h[level - 1], wr = g.w[level - 1];
+  const int kx0 = blockIdx.x * WV_IX, ky0 = blockIdx.y * WV_IY;
+  float* base = ws + (size_t)blockIdx.z * g.chan_floats;
+  const float t_da = stats[blockIdx.z].thr[level][0], t_ad = stats[blockIdx.z].thr[level][1],
+              t_dd = stats[blockIdx.z].thr[level][2];
+  const int i_y0 = ky0 / 2;                                    // first coefficient row of the tile
+  // 1. along x: (app, ad) -> lo, (da, dd) -> hi at the tile's coefficient rows
+  for (int item = threadIdx.x; item < RC * (WV_IX / WV_RO); item += 256) {
+    const int r = item / (WV_IX / WV_RO), ql = item - r * (WV_IX / WV_RO);
+    const int k0 = kx0 + ql * WV_RO, y = i_y0 + r;
+    float lo4[WV_RO] = {0.f, 0.f, 0.f, 0.f}, hi4[WV_RO] = {0.f, 0.f, 0.f, 0.f};
+    if (k0 < wr && y < hl) {
+      const int q = k0 / WV_RO;
+      const size_t ro = (size_t)y * wl;
+      const float* app = base + g.off_app[level] + ro;
+      const float* da = base + g.off_det[level][0] + ro;
+      const float* ad = base + g.off_det[level][1] + ro;
+      const float* dd = base + g.off_det[level][2] + ro;
+      float va[NE], vad[NE], vda[NE], vdd[NE];
+#pragma unroll
+      for (int e = 0; e < NE; ++e) {
+        const int i = 2 * q + e;
+        const bool ok = i < wl;
+        va[e] = ok ? app[i] : 0.f;
+        vad[e] = ok ? wv_soft(ad[i], t_ad) : 0.f;
+        vda[e] = ok ? wv_soft(da[i], t_da) : 0.f;
+        vdd[e] = ok ? wv_soft(dd[i], t_dd) : 0.f;
+      }
+#pragma unroll
+      for (int o = 0; o < WV_RO; ++o) {
+        lo4[o] = idwt4<WAVE>(va, vad, o);
+        hi4[o] = idwt4<WAVE>(vda, vdd, o);
+      }
+    }
+    *reinterpret_cast<float4*>(&s_lo[r][ql * WV_RO]) = make_float4(lo4[0], lo4[1], lo4[2], lo4[3]);
+    *reinterpret_cast<float4*>(&s_hi[r][ql * WV_RO]) = make_float4(hi4[0], hi4[1], hi4[2], hi4[3]);
+  }
+  __syncthreads();
+  // 2. along y: thread = (column, half of the tile's 8 groups of 4 output rows); rows y >= hl were stored as 0
+  const int xl = threadIdx.x % WV_IX, half = threadIdx.x / WV_IX, x = kx0 + xl;
+  if (x >= wr) return;
+  float* out = base + (level == 1 ? g.off_plane : g.off_app[level - 1]) + x;
+#pragma unroll
+  for (int qq = 0; qq < WV_IY / WV_RO / 2; ++qq) {
+    const int ql = half * (WV_IY / WV_RO / 2) + qq;            // group of 4 output rows inside the tile
+    const int k0 = ky0 + ql * WV_RO;
+    if (k0 >= hr) break;
+    float vl[NE], vh[NE];
+#pragma unroll
+    for (int e = 0; e < NE; ++e) {
+      vl[e] = s_lo[2 * ql + e][xl];
+      vh[e] = s_hi[2 * ql + e][xl];
+    }
+#pragma unroll
+    for (int o = 0; o < WV_RO; ++o) {
+      if (k0 + o >= hr) break;
+      out[(size_t)(k0 + o) * wr] = idwt4<WAVE>(vl, vh, o);
+    }
   }
 }
 
@@ -731,6 +927,7 @@ int run_wavelet(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, int ki
     }
     count_launch();
     static const bool generic = [] { const char* e = getenv("B2D_WV_GENERIC"); return e && e[0] == '1'; }();
+    static const bool fused = [] { const char* e = getenv("B2D_WV_FUSED"); return !(e && e[0] == '0'); }();
     const bool db1 = sp.wavelet == B2D_WAVELET_DB1;
     auto cdiv = [](int a, int b) { return (unsigned)((a + b - 1) / b); };
     for (int l = 1; l <= g.L; ++l) {
@@ -738,6 +935,12 @@ int run_wavelet(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, int ki
       if (generic) {
         k_dwt_rows<<<dim3(blocks((size_t)g.h[l - 1] * g.w[l]), 1, planes), 256, 0, st>>>(g, ws, l, in_off);
         k_dwt_cols<<<dim3(blocks((size_t)g.h[l] * g.w[l]), 1, planes), 256, 0, st>>>(g, ws, l);
+      } else if (fused) {
+        const dim3 gf(cdiv(g.w[l], WV_FOX), cdiv(g.h[l], WV_FOY), planes);
+        if (db1) k_dwt2_t<B2D_WAVELET_DB1><<<gf, 256, 0, st>>>(g, ws, stats, l, in_off);
+        else k_dwt2_t<B2D_WAVELET_BIOR15><<<gf, 256, 0, st>>>(g, ws, stats, l, in_off);
+        count_launch();
+        continue;                                              // band energies are summed inside
       } else {
         const dim3 gr(cdiv(cdiv(g.w[l], WV_RO), 256), (unsigned)g.h[l - 1], planes);
         const dim3 gc(cdiv(g.w[l], 256), cdiv(g.h[l], WV_RO), planes);
@@ -757,6 +960,12 @@ int run_wavelet(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, int ki
       if (generic) {
         k_idwt_rows<<<dim3(blocks((size_t)g.h[l] * g.w[l - 1]), 1, planes), 256, 0, st>>>(g, ws, stats, l);
         k_idwt_cols<<<dim3(blocks((size_t)g.h[l - 1] * g.w[l - 1]), 1, planes), 256, 0, st>>>(g, ws, l);
+      } else if (fused) {
+        const dim3 gi(cdiv(g.w[l - 1], WV_IX), cdiv(g.h[l - 1], WV_IY), planes);
+        if (db1) k_idwt2_t<B2D_WAVELET_DB1><<<gi, 256, 0, st>>>(g, ws, stats, l);
+        else k_idwt2_t<B2D_WAVELET_BIOR15><<<gi, 256, 0, st>>>(g, ws, stats, l);
+        count_launch();
+        continue;
       } else {
         const dim3 gr(cdiv(cdiv(g.w[l - 1], WV_RO), 256), (unsigned)g.h[l], planes);
         const dim3 gc(cdiv(g.w[l - 1], 256), cdiv(g.h[l - 1], WV_RO), planes);

@@ -112,7 +112,8 @@ def test_haar_fast_path_equals_general_path(cuda, tmp_path):
 
 
 def test_specialised_wavelet_kernels_equal_generic(cuda, tmp_path):
-    """The register-window kernels (compile-time taps, zero taps dropped, 4 outputs per thread) against
+    """The fused 2-D level kernels (default) and the register-window kernels (compile-time taps, zero taps
+    dropped, 4 outputs per thread; B2D_WV_FUSED=0) against
     the generic per-output kernels (B2D_WV_GENERIC=1), bior1.5 and db1 / auto levels, odd sizes included:
     same accumulation order, so the uint8 outputs must be identical."""
     import os
@@ -133,10 +134,12 @@ for h, w in ((37, 53), (120, 200), (375, 500), (601, 333)):
 np.savez(sys.argv[2], **out)
 """
     outs = {}
-    for tag, env in (("fast", {"B2D_HAAR": "0"}), ("generic", {"B2D_HAAR": "0", "B2D_WV_GENERIC": "1"})):
+    for tag, env in (("fast", {"B2D_HAAR": "0"}), ("unfused", {"B2D_HAAR": "0", "B2D_WV_FUSED": "0"}),
+                     ("generic", {"B2D_HAAR": "0", "B2D_WV_GENERIC": "1"})):
         path = str(tmp_path / (tag + ".npz"))
         subprocess.run([sys.executable, "-c", script, root, path], check=True, env=dict(os.environ, **env), timeout=600)
         outs[tag] = dict(np.load(path))
     assert set(outs["fast"]) == set(outs["generic"]) and len(outs["fast"]) == 16
-    for key, a in outs["fast"].items():
-        assert np.array_equal(a, outs["generic"][key]), (key, int((a != outs["generic"][key]).sum()))
+    for tag in ("fast", "unfused"):                              # fast = the fused 2-D kernels (rows + columns + energies)
+        for key, a in outs[tag].items():
+            assert np.array_equal(a, outs["generic"][key]), (tag, key, int((a != outs["generic"][key]).sum()))
