@@ -159,6 +159,14 @@ __global__ void __launch_bounds__(256) k_wv_color(ImageSet s, NoiseArgs na, WvGe
 // Products and sums are rounded separately (no FMA): pywt / NumPy do the same, and it
 // keeps coefficients that cancel exactly (duplicated border samples, flat regions)
 // exactly zero - _sigma_est_dwt drops exact zeros before taking the median.
+// The high-pass taps keep that rule.  The low-pass taps of the long filter (bior1.5: 10 taps, F > 2) accumulate
+// with FMA - half the instructions, one rounding less per tap, and no output that must be an exact
+// zero depends on them (dd, the band _sigma_est_dwt filters, is high-pass in both directions); db1 keeps
+// separate roundings so that the general path and the Haar fast path (b2d_haar.cu) agree.
+__device__ __forceinline__ float lo_acc(int F, float acc, float c, float x) {
+  return F > 2 ? fmaf(c, x, acc) : __fadd_rn(acc, __fmul_rn(c, x));
+}
+
 // pywt 'symmetric' (half-sample) extension
 __device__ __forceinline__ int sym_ext(int i, int n) {
   const int p = 2 * n;
@@ -182,11 +190,11 @@ __global__ void __launch_bounds__(256) k_dwt_rows(WvGeom g, float* ws, int level
     if (2 * i + 1 - (g.F - 1) >= 0 && 2 * i + 1 < w) {
 #pragma unroll
       for (int j = 0; j < WV_MAXF; ++j)
-        if (j < g.F) { const float x = row[2 * i + 1 - j]; a = __fadd_rn(a, __fmul_rn(g.dec_lo[j], x)); d = __fadd_rn(d, __fmul_rn(g.dec_hi[j], x)); }
+        if (j < g.F) { const float x = row[2 * i + 1 - j]; a = lo_acc(g.F, a, g.dec_lo[j], x); d = __fadd_rn(d, __fmul_rn(g.dec_hi[j], x)); }
     } else {
       for (int j = 0; j < g.F; ++j) {
         const float x = row[sym_ext(2 * i + 1 - j, w)];
-        a = __fadd_rn(a, __fmul_rn(g.dec_lo[j], x));
+        a = lo_acc(g.F, a, g.dec_lo[j], x);
         d = __fadd_rn(d, __fmul_rn(g.dec_hi[j], x));
       }
     }
@@ -212,9 +220,9 @@ __global__ void __launch_bounds__(256) k_dwt_cols(WvGeom g, float* ws, int level
     for (int j = 0; j < g.F; ++j) {
       const int y = sym_ext(2 * i + 1 - j, h);
       const float l = lo[(size_t)y * wo + x], hv = hi[(size_t)y * wo + x];
-      s_aa = __fadd_rn(s_aa, __fmul_rn(g.dec_lo[j], l));
+      s_aa = lo_acc(g.F, s_aa, g.dec_lo[j], l);
       s_da = __fadd_rn(s_da, __fmul_rn(g.dec_hi[j], l));
-      s_ad = __fadd_rn(s_ad, __fmul_rn(g.dec_lo[j], hv));
+      s_ad = lo_acc(g.F, s_ad, g.dec_lo[j], hv);
       s_dd = __fadd_rn(s_dd, __fmul_rn(g.dec_hi[j], hv));
     }
     aa[t] = s_aa; da[t] = s_da; ad[t] = s_ad; dd[t] = s_dd;
@@ -284,7 +292,7 @@ __global__ void __launch_bounds__(256) k_dwt_rows_t(WvGeom g, float* ws, int lev
 #pragma unroll
     for (int j = 0; j < F; ++j) {
       const float x = v[2 * o + F - 1 - j];
-      if (C::dec_lo(j) != 0.0f) a = __fadd_rn(a, __fmul_rn(C::dec_lo(j), x));
+      if (C::dec_lo(j) != 0.0f) a = lo_acc(F, a, C::dec_lo(j), x);
       if (C::dec_hi(j) != 0.0f) d = __fadd_rn(d, __fmul_rn(C::dec_hi(j), x));
     }
     lo[i0 + o] = a;
@@ -322,7 +330,7 @@ __global__ void __launch_bounds__(256) k_dwt_cols_t(WvGeom g, float* ws, int lev
 #pragma unroll
     for (int j = 0; j < F; ++j) {
       const float l = vl[2 * o + F - 1 - j], hv = vh[2 * o + F - 1 - j];
-      if (C::dec_lo(j) != 0.0f) { s_aa = __fadd_rn(s_aa, __fmul_rn(C::dec_lo(j), l)); s_ad = __fadd_rn(s_ad, __fmul_rn(C::dec_lo(j), hv)); }
+      if (C::dec_lo(j) != 0.0f) { s_aa = lo_acc(F, s_aa, C::dec_lo(j), l); s_ad = lo_acc(F, s_ad, C::dec_lo(j), hv); }
       if (C::dec_hi(j) != 0.0f) { s_da = __fadd_rn(s_da, __fmul_rn(C::dec_hi(j), l)); s_dd = __fadd_rn(s_dd, __fmul_rn(C::dec_hi(j), hv)); }
     }
     const size_t r = (size_t)(i0 + o) * wo;
@@ -427,15 +435,19 @@ __global__ void __launch_bounds__(256) k_dwt2_t(WvGeom g, float* ws, WvStats* st
   const int nout_y = min(WV_FOY, ho - oy0);
   const int rows = 2 * nout_y + F - 2;                         // input rows 2 oy0 + 2 - F ... of this tile
   const int ylo = 2 * oy0 + 2 - F;
-  // 1. along x into shared memory: item = (input row, group of 4 coefficients)
-  for (int item = threadIdx.x; item < rows * (WV_FOX / WV_RO); item += 256) {
-    const int r = item / (WV_FOX / WV_RO), q = item - r * (WV_FOX / WV_RO);
-    const int i0 = ox0 + q * WV_RO;
-    if (i0 >= wo) continue;
-    const float* row = in + (size_t)sym_ext(ylo + r, h) * w;
-    const int xlo = 2 * i0 + 2 - F;
+  // 1. along x into shared memory: a thread keeps its group of 4 coefficients (q) and walks the input rows
+  // r = tid / 16, + 16, ...; everything that depends on q only is computed once
+  const int q = threadIdx.x % (WV_FOX / WV_RO), i0 = ox0 + q * WV_RO;
+  const int xlo = 2 * i0 + 2 - F;
+  const bool x_inside = xlo >= 0 && xlo + NIN <= w;
+  const bool one_fold = h >= F;                                // |overshoot| <= F - 2 < h: a single reflection
+  for (int r = threadIdx.x / (WV_FOX / WV_RO); r < rows && i0 < wo; r += 256 / (WV_FOX / WV_RO)) {
+    int yy = ylo + r;
+    if (one_fold) yy = yy < 0 ? -1 - yy : (yy >= h ? 2 * h - 1 - yy : yy);
+    else yy = sym_ext(yy, h);
+    const float* row = in + (unsigned)(yy * w);
     float v[NIN];
-    if (xlo >= 0 && xlo + NIN <= w) {
+    if (x_inside) {
       if (NIN % 4 == 0 && (reinterpret_cast<uintptr_t>(row + xlo) & 15u) == 0) {
 #pragma unroll
         for (int e = 0; e < NIN / 4; ++e) {
@@ -457,7 +469,7 @@ __global__ void __launch_bounds__(256) k_dwt2_t(WvGeom g, float* ws, WvStats* st
 #pragma unroll
       for (int j = 0; j < F; ++j) {
         const float x = v[2 * o + F - 1 - j];
-        if (C::dec_lo(j) != 0.0f) a[o] = __fadd_rn(a[o], __fmul_rn(C::dec_lo(j), x));
+        if (C::dec_lo(j) != 0.0f) a[o] = lo_acc(F, a[o], C::dec_lo(j), x);
         if (C::dec_hi(j) != 0.0f) d[o] = __fadd_rn(d[o], __fmul_rn(C::dec_hi(j), x));
       }
     }
@@ -472,9 +484,8 @@ __global__ void __launch_bounds__(256) k_dwt2_t(WvGeom g, float* ws, WvStats* st
     float vl[NIN], vh[NIN];
 #pragma unroll
     for (int e = 0; e < NIN; ++e) {
-      const int r = min(2 * grp * WV_RO + e, rows - 1);        // rows past the tile's last output are never used
-      vl[e] = s_lo[r][xl];
-      vh[e] = s_hi[r][xl];
+      vl[e] = s_lo[2 * grp * WV_RO + e][xl];                   // rows past `rows` hold stale data and feed only
+      vh[e] = s_hi[2 * grp * WV_RO + e][xl];                   // outputs i >= ho, which are dropped below
     }
     float* aa = base + g.off_app[level] + x;
     float* da = base + g.off_det[level][0] + x;
@@ -488,10 +499,10 @@ __global__ void __launch_bounds__(256) k_dwt2_t(WvGeom g, float* ws, WvStats* st
 #pragma unroll
       for (int j = 0; j < F; ++j) {
         const float l = vl[2 * o + F - 1 - j], hv = vh[2 * o + F - 1 - j];
-        if (C::dec_lo(j) != 0.0f) { s_aa = __fadd_rn(s_aa, __fmul_rn(C::dec_lo(j), l)); s_ad = __fadd_rn(s_ad, __fmul_rn(C::dec_lo(j), hv)); }
+        if (C::dec_lo(j) != 0.0f) { s_aa = lo_acc(F, s_aa, C::dec_lo(j), l); s_ad = lo_acc(F, s_ad, C::dec_lo(j), hv); }
         if (C::dec_hi(j) != 0.0f) { s_da = __fadd_rn(s_da, __fmul_rn(C::dec_hi(j), l)); s_dd = __fadd_rn(s_dd, __fmul_rn(C::dec_hi(j), hv)); }
       }
-      const size_t r = (size_t)i * wo;
+      const unsigned r = (unsigned)(i * wo);
       aa[r] = s_aa; da[r] = s_da; ad[r] = s_ad; dd[r] = s_dd;
       e_da += (double)s_da * s_da;
       e_ad += (double)s_ad * s_ad;

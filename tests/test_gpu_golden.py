@@ -27,6 +27,7 @@ def test_cuda_path_matches_golden_manifest(cuda):
         manifest = json.load(f)
     same_libs = G.versions() == manifest["versions"]
     n_exact = n_tol = 0
+    failures = []
     for cid, img, spec, fields in G.cases():
         entry = manifest["cases"][cid]
         got = api.apply(torch.from_numpy(img[None]).to(cuda), spec, fields=_fields_to_dev(fields, cuda)).cpu().numpy()[0]
@@ -40,9 +41,21 @@ def test_cuda_path_matches_golden_manifest(cuda):
         d = (got.astype(int) - want.astype(int))
         if entry["class"] == "lsb":
             # wavelet: the reference truncates a float64 that sits on integers for block-constant areas (see
-            # tests/test_gpu_wavelet.py::check), so only the magnitude is tight there; bilateral: < 0.2 % of pixels
+            # tests/test_gpu_wavelet.py::check), so only the magnitude is tight there; bilateral: < 0.2 % of pixels.
+            # Natural image + wavelet: the reference's sigma = median(|dd_1| != 0) counts float64 rounding-noise
+            # coefficients (|d| ~ 1e-17 where the pixel differences cancel algebraically; 8-12 % of the non-zero
+            # chroma coefficients of this crop) as non-zero, and at one level BayesShrink's dd threshold
+            # var / sqrt(dvar - var) sits 5 % from its pole: which of those coefficients cancel exactly is decided by
+            # the last bit of float64 arithmetic, no fp32 path reproduces it, and the threshold moves by ~10 %
+            # (DESIGN.md section 4).  Allowed there: <= 2 LSB, > 1 LSB on < 1 % of the pixels.
             frac = 0.3 if "wavelet" in spec else 2e-3
-            assert np.abs(d).max() <= 1 and (d != 0).mean() < frac, (cid, int(np.abs(d).max()), float((d != 0).mean()))
+            a = np.abs(d)
+            if "wavelet" in spec and cid.startswith("natural"):
+                ok = a.max() <= 2 and (a > 1).mean() < 1e-2 and (a > 0).mean() < frac
+            else:
+                ok = a.max() <= 1 and (a > 0).mean() < frac
+            if not ok:
+                failures.append((cid, int(a.max()), float((a > 0).mean()), float((a > 1).mean())))
         elif entry["class"] == "brownian":
             m = d % 256
             bad = m != 0
@@ -53,4 +66,5 @@ def test_cuda_path_matches_golden_manifest(cuda):
         else:                                             # periodic: last-ulp differences of fp64 sin
             assert (d != 0).mean() <= 1e-5, (cid, int((d != 0).sum()))
         n_tol += 1
+    assert not failures, failures
     assert n_exact >= 100 and n_tol >= 60
