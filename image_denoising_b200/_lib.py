@@ -42,7 +42,8 @@ class B2DError(RuntimeError):
 
 EXPORTS = ["b2d_parse_spec", "b2d_plan_create", "b2d_plan_workspace_bytes", "b2d_plan_destroy", "b2d_run",
            "b2d_run_host", "b2d_host_register", "b2d_host_unregister", "b2d_noise_field", "b2d_stats", "b2d_lab_convert",
-           "b2d_poisson_table", "b2d_gamma_table", "b2d_blob_shape", "b2d_blob_prep", "b2d_launch_count", "b2d_reset_launch_count", "b2d_last_error", "b2d_version"]
+           "b2d_poisson_table", "b2d_gamma_table", "b2d_blob_shape", "b2d_blob_prep", "b2d_jpeg_info", "b2d_jpeg_create", "b2d_jpeg_decode", "b2d_jpeg_destroy", "b2d_jpeg_entropy",
+           "b2d_launch_count", "b2d_reset_launch_count", "b2d_last_error", "b2d_version"]
 
 _lib = None
 
@@ -87,13 +88,22 @@ def lib():
                                                       ctypes.POINTER(ctypes.c_int)]
     L.b2d_blob_prep.argtypes = [vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, ctypes.c_int, ctypes.c_int,
                                 ctypes.c_double, ctypes.POINTER(ctypes.c_double), vp, ctypes.c_int, vp]
+    ip = ctypes.POINTER(ctypes.c_int)
+    L.b2d_jpeg_info.argtypes = [vp, sz, ip, ip, ip, ip, ip]
+    L.b2d_jpeg_create.argtypes = [ctypes.POINTER(vp), ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int]
+    L.b2d_jpeg_decode.argtypes = [vp, ctypes.c_int, ctypes.POINTER(vp), ctypes.POINTER(sz), vp, vp]
+    L.b2d_jpeg_destroy.argtypes = [vp]
+    L.b2d_jpeg_entropy.argtypes = [vp, sz, vp, sz, ip, ip]
+    L.b2d_jpeg_entropy.restype = ctypes.c_int
+    L.b2d_jpeg_destroy.restype = None
     L.b2d_launch_count.restype = u64
     L.b2d_reset_launch_count.restype = None
     L.b2d_last_error.restype = ctypes.c_char_p
     L.b2d_version.restype = ctypes.c_char_p
     for name in ("b2d_parse_spec", "b2d_plan_create", "b2d_plan_workspace_bytes", "b2d_run", "b2d_run_host",
                  "b2d_host_register", "b2d_host_unregister", "b2d_noise_field", "b2d_stats", "b2d_lab_convert",
-                 "b2d_poisson_table", "b2d_gamma_table", "b2d_blob_shape", "b2d_blob_prep"):
+                 "b2d_poisson_table", "b2d_gamma_table", "b2d_blob_shape", "b2d_blob_prep", "b2d_jpeg_info", "b2d_jpeg_create",
+                 "b2d_jpeg_decode"):
         getattr(L, name).restype = ctypes.c_int
     _lib = L
     return L

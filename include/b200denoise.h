@@ -185,6 +185,27 @@ int b2d_blob_shape(int h, int w, int target_size, int max_size, double* im_scale
 int b2d_blob_prep(const uint8_t* d_in, int n, int h, int w, float* d_out, int blob_h, int blob_w,
                   double im_scale, const double* pixel_means, const uint8_t* d_flip, int flags, void* cuda_stream);
 
+/* SURVEY 8(f) f2 - the stage in front of the path: `cv2.imread(path)` (lib/model/test.py:191,
+ *   lib/roi_data_layer/minibatch.py:85, and again inside most closures: minibatch.py:206,256,377,...) for baseline
+ *   JPEG streams.  cv2.imread = libjpeg-turbo defaults (JDCT_ISLOW, fancy upsampling, YCbCr -> BGR); the result is
+ *   bit-exact with cv2.imdecode(IMREAD_COLOR).  Huffman decoding runs on `host_threads` host threads (0 = all cores),
+ *   dequantisation + IDCT + chroma upsampling + colour conversion on the GPU.
+ *   b2d_jpeg_info   : frame header of one stream (any pointer may be NULL).
+ *   b2d_jpeg_create : decoder for batches of up to max_n images of exactly h x w (owns pinned staging + device scratch).
+ *   b2d_jpeg_decode : data[i] / len[i] = the i-th file's bytes (host); d_out = n x h x w x 3 uint8 BGR on the device,
+ *                     written asynchronously on cuda_stream.  Sampling 4:4:4, 4:2:2 (h2v1), 4:2:0 and greyscale (returned
+ *                     as 3 equal channels, like IMREAD_COLOR), restart intervals; progressive / arithmetic / 12-bit /
+ *                     CMYK streams fail with B2D_ERR_UNSUPPORTED - there is no fallback decoder. */
+typedef struct b2d_jpeg b2d_jpeg;
+int b2d_jpeg_info(const uint8_t* data, size_t len, int* h, int* w, int* components, int* hsamp, int* vsamp);
+int b2d_jpeg_create(b2d_jpeg** out, int device, int max_n, int h, int w, int host_threads);
+int b2d_jpeg_decode(b2d_jpeg* dec, int n, const uint8_t* const* data, const size_t* len, uint8_t* d_out, void* cuda_stream);
+void b2d_jpeg_destroy(b2d_jpeg* dec);
+/* host-only hook (no GPU needed): the quantised coefficients the Huffman stage hands to the GPU - component after
+ * component, blocks in raster order over whole MCUs, 64 int16 per block in natural (row-major) order - for the CPU tests
+ * that compare it with oracle/jpeg.py::entropy_decode.  blocks_x / blocks_y: 3 ints each. */
+int b2d_jpeg_entropy(const uint8_t* data, size_t len, int16_t* h_coef, size_t capacity, int* blocks_x, int* blocks_y);
+
 /* Per-image result statistics gathered after the run (8(e): the only data
  * that ever crosses GPUs): checksum = sum of bytes * (1 + index mod 251)
  * mod 2^64 of d_out[i]; sse = sum (d_out - d_ref)^2 (for PSNR vs clean). */

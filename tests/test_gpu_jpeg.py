@@ -1,0 +1,68 @@
+"""GPU: the device JPEG stage (SURVEY 8(f) f2, b2d_jpeg_decode through the C ABI) against cv2.imdecode - the call the
+reference makes (cv2.imread, lib/model/test.py:191) - byte for byte, and against the pinned oracle."""
+import cv2
+import numpy as np
+import pytest
+import torch
+
+from conftest import synth_image
+from oracle import jpeg as J
+from test_oracle_jpeg import CASES, S420, S422, S444, encode, streams
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("tag,data", list(streams()), ids=lambda v: str(v) if not isinstance(v, bytes) else "")
+def test_single_streams_bit_exact(cuda, tag, data):
+    from image_denoising_b200 import jpeg
+    want = cv2.imdecode(np.frombuffer(data, np.uint8), cv2.IMREAD_COLOR)
+    got = jpeg.imdecode_batch([data], cuda).cpu().numpy()[0]
+    assert got.shape == want.shape
+    assert np.array_equal(got, want), (tag, int((got != want).sum()))
+    assert np.array_equal(got, J.decode(data))
+
+
+@pytest.mark.parametrize("shape", [(375, 500), (600, 1000), (601, 999)])
+def test_mixed_batch_bit_exact(cuda, shape):
+    """One batch, every image its own quality / sampling / restart interval (VOC files differ in all three)."""
+    from image_denoising_b200 import jpeg
+    h, w = shape
+    datas = []
+    for i, (q, samp, rst) in enumerate([(90, S420, 0), (75, S444, 0), (60, S422, 4), (95, S420, 11), (35, S420, 0), (85, None, 1)]):
+        datas.append(encode(synth_image(h, w, 50 + i, "smooth" if i % 2 == 0 else "uniform"), q, samp, rst))
+    datas.append(encode(synth_image(h, w, 9, "smooth")[..., 1], 80))                # greyscale file
+    got = jpeg.imdecode_batch(datas, cuda).cpu().numpy()
+    for i, d in enumerate(datas):
+        want = cv2.imdecode(np.frombuffer(d, np.uint8), cv2.IMREAD_COLOR)
+        assert np.array_equal(got[i], want), (shape, i, int((got[i] != want).sum()))
+    again = jpeg.imdecode_batch(datas[:3], cuda).cpu().numpy()                      # decoder reuse, smaller batch
+    assert np.array_equal(again, got[:3])
+
+
+def test_natural_image_and_feeds_the_path(cuda):
+    """A natural image (the crop of the reference's data/demo/000456.jpg kept under tests/golden) re-encoded, decoded on
+    the device and handed straight to the corrupt -> denoise path: same bytes as cv2.imdecode + the same path."""
+    import golden_cases as G
+    from image_denoising_b200 import api, jpeg
+    img = G.inputs()["natural_120x160"]
+    datas = [encode(img, q, s) for q, s in ((92, S420), (70, S444))]
+    dev = jpeg.imdecode_batch(datas, cuda)
+    host = np.stack([cv2.imdecode(np.frombuffer(d, np.uint8), cv2.IMREAD_COLOR) for d in datas])
+    assert np.array_equal(dev.cpu().numpy(), host)
+    a = api.apply(dev, "periodic_median_var100")
+    b = api.apply(torch.from_numpy(host).to(cuda), "periodic_median_var100")
+    assert torch.equal(a, b)
+
+
+def test_errors_are_loud(cuda):
+    from image_denoising_b200 import _lib, jpeg
+    img = synth_image(32, 48, 1, "smooth")
+    good, other = encode(img, 90), encode(synth_image(40, 48, 1, "smooth"), 90)
+    with pytest.raises(_lib.B2DError):
+        jpeg.imdecode_batch([good, other], cuda)                                    # sizes differ inside one batch
+    prog = encode(img, 90, None, 0, (cv2.IMWRITE_JPEG_PROGRESSIVE, 1))
+    with pytest.raises(_lib.B2DError) as e:
+        jpeg.imdecode_batch([prog], cuda)
+    assert e.value.code == _lib.ERR_UNSUPPORTED
+    ok = jpeg.imdecode_batch([good], cuda).cpu().numpy()[0]                         # decoder still usable afterwards
+    assert np.array_equal(ok, cv2.imdecode(np.frombuffer(good, np.uint8), cv2.IMREAD_COLOR))
