@@ -19,6 +19,7 @@
 #include "b2d_plan.h"
 
 #include <atomic>
+#include <chrono>
 #include <algorithm>
 #include <cstring>
 #include <new>
@@ -46,6 +47,7 @@ struct HuffTab {
   uint16_t fast[512];            // 9-bit look-ahead: (length << 8) | symbol, 0 = longer code
   int maxcode[18], valptr[17], mincode[17];
   uint8_t vals[256];
+  int16_t fast_ac[512];          // AC tables: (value << 8) | (run << 4) | (code length + magnitude bits) when both fit in 9 bits
   bool present = false;
 };
 
@@ -69,6 +71,17 @@ static bool build_huff(HuffTab& t, const uint8_t* counts, const uint8_t* symbols
   }
   t.maxcode[17] = 0x7fffffff;
   t.present = true;
+  // run / size / value of short AC codes in one lookup (the common case: small coefficients, short codes)
+  for (int i = 0; i < 512; ++i) {
+    t.fast_ac[i] = 0;
+    const uint16_t f = t.fast[i];
+    if (!f) continue;
+    const int l = f >> 8, rs = f & 0xff, run = rs >> 4, mag = rs & 15;
+    if (mag == 0 || l + mag > 9) continue;
+    int v = ((i << l) & 511) >> (9 - mag);
+    if (v < (1 << (mag - 1))) v += (int)((~0u) << mag) + 1;
+    if (v >= -128 && v <= 127) t.fast_ac[i] = (int16_t)(v * 256 + run * 16 + (l + mag));
+  }
   return k == nsym;
 }
 
@@ -79,6 +92,20 @@ struct BitReader {
   int n = 0;
   bool marker = false;           // fill() ran into a marker: zeros are fed from here on (as libjpeg does)
   void fill() {
+    if (!marker && pos + 8 <= len && n <= 56) {        // 8 bytes at once when none of them is 0xFF
+      uint64_t w;
+      memcpy(&w, d + pos, 8);
+      w = __builtin_bswap64(w);
+      const uint64_t x = ~w;
+      if (!((x - 0x0101010101010101ull) & ~x & 0x8080808080808080ull)) {
+        const int take = (64 - n) >> 3;
+        const uint64_t keep = take == 8 ? ~0ull : ~(~0ull >> (8 * take));
+        acc |= (w & keep) >> n;
+        pos += take;
+        n += 8 * take;
+        return;
+      }
+    }
     while (n <= 56) {
       uint32_t b = 0;
       if (!marker && pos < len) {
@@ -253,6 +280,15 @@ static int entropy_decode(const uint8_t* d, size_t len, const Parsed& P, const J
             if (t) pred[c] += receive_extend(br, t);
             blk[0] = (int16_t)pred[c];
             for (int k = 1; k < 64;) {
+              if (br.n < 16) br.fill();
+              const int fa = ac.fast_ac[br.peek(9)];
+              if (fa) {
+                k += (fa >> 4) & 15;
+                if (k > 63) { msg = "AC run past the block"; return B2D_ERR_INVALID; }
+                br.skip(fa & 15);
+                blk[kZigzag[k++]] = (int16_t)(fa >> 8);
+                continue;
+              }
               const int rs = decode_sym(br, ac);
               if (rs < 0) { msg = "bad AC code"; return B2D_ERR_INVALID; }
               const int r = rs >> 4, s = rs & 15;
@@ -532,50 +568,87 @@ int b2d_jpeg_decode(b2d_jpeg* D, int n, const uint8_t* const* data, const size_t
   if (n == 0) return B2D_OK;
   CKJ(cudaSetDevice(D->device));
   if (D->pending) { CKJ(cudaEventSynchronize(D->uploaded)); D->pending = false; }   // pinned staging is free again
+  // Host threads decode images in order; the calling thread uploads and launches chunk after chunk as soon as a
+  // chunk's images are done, so the copies and the kernels run under the Huffman decoding of the following chunks.
+  constexpr int CH = 16;
   std::vector<int> rc(n, B2D_OK);
   std::vector<std::string> msg(n);
+  std::vector<size_t> used(n, 0);
+  std::vector<std::atomic<int>> done(n);
+  for (auto& f : done) f.store(0, std::memory_order_relaxed);
   std::atomic<int> next(0);
+  std::atomic<bool> abort(false);
+  auto decode_one = [&](int i, Parsed* P) {
+    *P = Parsed();
+    if (!data[i]) { rc[i] = B2D_ERR_INVALID; msg[i] = "null stream"; return; }
+    rc[i] = parse_jpeg(data[i], len[i], *P, msg[i], false);
+    if (rc[i] != B2D_OK) return;
+    if (P->h != D->h || P->w != D->w) {
+      rc[i] = B2D_ERR_INVALID;
+      msg[i] = "image is " + std::to_string(P->h) + " x " + std::to_string(P->w) + ", decoder was created for " +
+               std::to_string(D->h) + " x " + std::to_string(D->w);
+      return;
+    }
+    JpegImg& J = D->h_desc[i];
+    layout(*P, J);
+    used[i] = (size_t)J.coef_off[J.ncomp - 1] + (size_t)J.bx[J.ncomp - 1] * J.by[J.ncomp - 1] * 64;
+    rc[i] = entropy_decode(data[i], len[i], *P, J, D->h_coef + (size_t)i * D->coef_per_img, msg[i]);
+  };
   auto work = [&]() {
     Parsed* P = new (std::nothrow) Parsed();
-    if (!P) return;
     for (int i = next.fetch_add(1); i < n; i = next.fetch_add(1)) {
-      *P = Parsed();
-      if (!data[i]) { rc[i] = B2D_ERR_INVALID; msg[i] = "null stream"; continue; }
-      rc[i] = parse_jpeg(data[i], len[i], *P, msg[i], false);
-      if (rc[i] != B2D_OK) continue;
-      if (P->h != D->h || P->w != D->w) {
-        rc[i] = B2D_ERR_INVALID;
-        msg[i] = "image is " + std::to_string(P->h) + " x " + std::to_string(P->w) + ", decoder was created for " +
-                 std::to_string(D->h) + " x " + std::to_string(D->w);
-        continue;
-      }
-      layout(*P, D->h_desc[i]);
-      rc[i] = entropy_decode(data[i], len[i], *P, D->h_desc[i], D->h_coef + (size_t)i * D->coef_per_img, msg[i]);
+      if (!P) { rc[i] = B2D_ERR_INVALID; msg[i] = "out of host memory"; }
+      else if (!abort.load(std::memory_order_relaxed)) decode_one(i, P);
+      done[i].store(1, std::memory_order_release);
     }
     delete P;
   };
   const int nt = std::min(D->threads, n);
-  if (nt <= 1) {
-    work();
-  } else {
-    std::vector<std::thread> pool;
+  std::vector<std::thread> pool;
+  if (nt > 1)
     for (int t = 0; t < nt; ++t) pool.emplace_back(work);
-    for (auto& t : pool) t.join();
-  }
-  for (int i = 0; i < n; ++i)
-    if (rc[i] != B2D_OK) return fail(rc[i], "b2d_jpeg_decode: image %d: %s", i, msg[i].c_str());
   cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
-  CKJ(cudaMemcpyAsync(D->d_desc, D->h_desc, sizeof(JpegImg) * n, cudaMemcpyHostToDevice, st));
-  CKJ(cudaMemcpyAsync(D->d_coef, D->h_coef, D->coef_per_img * n * sizeof(int16_t), cudaMemcpyHostToDevice, st));
-  CKJ(cudaEventRecord(D->uploaded, st));
-  D->pending = true;
   const size_t hp = ((size_t)D->h + 15) / 16 * 16, wp = ((size_t)D->w + 15) / 16 * 16;
   const unsigned max_blocks = (unsigned)(hp * wp / 64);
-  k_jpeg_idct<<<dim3((max_blocks + 127) / 128, 3, n), 128, 0, st>>>(D->d_desc, D->d_coef, D->d_planes, D->coef_per_img, D->plane_per_img);
-  k_jpeg_color<<<dim3((D->w + 511) / 512, D->h, n), 128, 0, st>>>(D->d_desc, D->d_planes, D->plane_per_img, d_out, D->h, D->w);
-  count_launch(); count_launch();
-  const cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) return fail_cuda(e, "jpeg kernels");
+  Parsed* mine = nt > 1 ? nullptr : new (std::nothrow) Parsed();
+  int status = B2D_OK, bad = -1;
+  cudaError_t ce = cudaSuccess;
+  for (int first = 0; first < n && status == B2D_OK && ce == cudaSuccess; first += CH) {
+    const int cnt = std::min(CH, n - first);
+    size_t width = 0;
+    for (int i = first; i < first + cnt; ++i) {
+      if (nt > 1) {
+        while (!done[i].load(std::memory_order_acquire)) std::this_thread::sleep_for(std::chrono::microseconds(30));   // not a spin: every core is decoding
+      } else if (mine) {
+        decode_one(i, mine);
+      } else {
+        rc[i] = B2D_ERR_INVALID; msg[i] = "out of host memory";
+      }
+      if (rc[i] != B2D_OK && status == B2D_OK) { status = rc[i]; bad = i; }
+      width = std::max(width, used[i]);
+    }
+    if (status != B2D_OK) break;
+    const size_t pitch = D->coef_per_img * sizeof(int16_t);
+    ce = cudaMemcpyAsync(D->d_desc + first, D->h_desc + first, sizeof(JpegImg) * cnt, cudaMemcpyHostToDevice, st);
+    if (ce == cudaSuccess)
+      ce = cudaMemcpy2DAsync(D->d_coef + (size_t)first * D->coef_per_img, pitch, D->h_coef + (size_t)first * D->coef_per_img, pitch,
+                             width * sizeof(int16_t), cnt, cudaMemcpyHostToDevice, st);
+    if (ce != cudaSuccess) break;
+    k_jpeg_idct<<<dim3((max_blocks + 127) / 128, 3, cnt), 128, 0, st>>>(D->d_desc + first, D->d_coef + (size_t)first * D->coef_per_img,
+                                                                       D->d_planes + (size_t)first * D->plane_per_img,
+                                                                       D->coef_per_img, D->plane_per_img);
+    k_jpeg_color<<<dim3((D->w + 511) / 512, D->h, cnt), 128, 0, st>>>(D->d_desc + first, D->d_planes + (size_t)first * D->plane_per_img,
+                                                                     D->plane_per_img, d_out + (size_t)first * D->h * D->w * 3, D->h, D->w);
+    count_launch(); count_launch();
+    ce = cudaGetLastError();
+  }
+  if (status != B2D_OK || ce != cudaSuccess) abort.store(true);
+  for (auto& t : pool) t.join();
+  delete mine;
+  cudaEventRecord(D->uploaded, st);                            // the pinned staging is busy until this point of the stream
+  D->pending = true;
+  if (status != B2D_OK) return fail(status, "b2d_jpeg_decode: image %d: %s", bad, msg[bad].c_str());
+  if (ce != cudaSuccess) return fail_cuda(ce, "b2d_jpeg_decode upload / kernels");
   return B2D_OK;
 }
 

@@ -60,8 +60,8 @@ class Decoder:
             out = torch.empty((n, self.h, self.w, 3), dtype=torch.uint8, device=self.device)
         elif out.dtype != torch.uint8 or tuple(out.shape) != (n, self.h, self.w, 3) or not out.is_contiguous() or out.device != self.device:
             raise ValueError("out must be a contiguous uint8 tensor of shape (%d, %d, %d, 3) on %s" % (n, self.h, self.w, self.device))
-        keep = [(ctypes.c_uint8 * len(s)).from_buffer_copy(s) for s in streams]
-        ptrs = (ctypes.c_void_p * max(n, 1))(*[ctypes.cast(b, ctypes.c_void_p) for b in keep])
+        keep = [bytes(s) for s in streams]                       # no copy for bytes objects; the pointers below borrow them
+        ptrs = (ctypes.c_void_p * max(n, 1))(*[ctypes.cast(ctypes.c_char_p(b), ctypes.c_void_p) for b in keep])
         lens = (ctypes.c_size_t * max(n, 1))(*[len(s) for s in streams])
         stream = torch.cuda.current_stream(self.device).cuda_stream
         _lib.check(self.L.b2d_jpeg_decode(self.handle, n, ptrs, lens, ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(stream)))

@@ -33,6 +33,42 @@ def _load(entry):
     return img
 
 
+class _JpegStream:
+    """A not-yet-decoded JPEG file: bytes + the frame size from its header (decoded on the GPU)."""
+
+    def __init__(self, data):
+        from . import jpeg
+        self.data = data
+        h, w = jpeg.info(data)[:2]
+        self.shape = (h, w, 3)
+
+
+def _load_for_device(entry):
+    """`_load`, except that JPEG files stay encoded: `cv2.imread` (minibatch.py:85) then happens on the GPU, bit-exact."""
+    im = entry['image']
+    if isinstance(im, np.ndarray):
+        return im
+    if str(im).lower().endswith((".jpg", ".jpeg")):
+        with open(im, "rb") as f:
+            return _JpegStream(f.read())
+    return _load(entry)
+
+
+def _to_device_batch(items, dev):
+    """list of ndarrays / _JpegStream of one shape -> (n, h, w, 3) uint8 CUDA tensor."""
+    import torch
+    from . import jpeg
+    enc = [k for k, it in enumerate(items) if isinstance(it, _JpegStream)]
+    if len(enc) == len(items):
+        return jpeg.imdecode_batch([it.data for it in items], dev)
+    batch = torch.empty((len(items),) + tuple(items[0].shape), dtype=torch.uint8, device=dev)
+    raw = [k for k in range(len(items)) if k not in enc]
+    batch[raw] = torch.from_numpy(np.ascontiguousarray(np.stack([items[k] for k in raw]))).to(dev)
+    if enc:
+        batch[enc] = jpeg.imdecode_batch([items[k].data for k in enc], dev)
+    return batch
+
+
 def corrupt_images(imgs, specs, indices, side="train", double_filter=False, rng=None):
     """imgs: list of HxWx3 uint8 BGR arrays -> list of corrupted + denoised uint8 arrays.
     Images of equal shape go to the GPU as one batch (per-image specs)."""
@@ -78,13 +114,15 @@ def _get_image_blob(roidb, scale_inds, double_filter=False):
     return im_list_to_blob(processed_ims), im_scales
 
 
-def _get_image_blob_device(roidb, scale_inds, double_filter=False):
+def _get_image_blob_device(roidb, scale_inds, double_filter=False, device_decode=False):
     """`_get_image_blob` with every step after the decode on the GPU: one H2D copy of
     the uint8 images, corrupt -> denoise (`b2d_run`), flip + mean subtraction + bilinear resize + NHWC
-    packing (`b2d_blob_prep`).  Returns (blob: (N, Hmax, Wmax, 3) float32 CUDA tensor, im_scales)."""
+    packing (`b2d_blob_prep`).  Returns (blob: (N, Hmax, Wmax, 3) float32 CUDA tensor, im_scales).
+    device_decode=True also moves `cv2.imread` of JPEG files to the GPU (8(f) f2: `b2d_jpeg_decode`; the H2D copy is
+    then the Huffman-decoded coefficients); a stream that decoder refuses raises, nothing falls back."""
     import torch
     from .blob import blob_shape, prep_blob_device
-    imgs = [_load(r) for r in roidb]
+    imgs = [_load_for_device(r) if device_decode else _load(r) for r in roidb]
     specs = [resolve_mix(r.get('noise_type', 'original'), "train", None) for r in roidb]
     indices = [int(r.get('index', i)) for i, r in enumerate(roidb)]
     targets = [cfg.TRAIN.SCALES[scale_inds[i]] for i in range(len(roidb))]
@@ -96,7 +134,7 @@ def _get_image_blob_device(roidb, scale_inds, double_filter=False):
     for i, im in enumerate(imgs):
         groups.setdefault((im.shape, targets[i]), []).append(i)
     for (shape, target), idx in groups.items():
-        batch = torch.from_numpy(np.ascontiguousarray(np.stack([imgs[i] for i in idx]))).to(dev)
+        batch = _to_device_batch([imgs[i] for i in idx], dev)
         consecutive = all(indices[idx[j]] == indices[idx[0]] + j for j in range(len(idx)))
         if consecutive:
             res = api.apply(batch, [specs[i] for i in idx], seed=cfg.RNG_SEED, first_index=indices[idx[0]])
@@ -120,15 +158,16 @@ def _get_image_blob_device(roidb, scale_inds, double_filter=False):
     return blob, [s[0] for s in shapes]
 
 
-def get_minibatch(roidb, num_classes, device_blob=False):
+def get_minibatch(roidb, num_classes, device_blob=False, device_decode=False):
     """Given a roidb, construct a minibatch sampled from it (minibatch.py:42-75).
-    device_blob=True keeps blobs['data'] on the GPU (built by `_get_image_blob_device`)."""
+    device_blob=True keeps blobs['data'] on the GPU (built by `_get_image_blob_device`); device_decode=True (with
+    device_blob) also decodes JPEG files there."""
     num_images = len(roidb)
     random_scale_inds = npr.randint(0, high=len(cfg.TRAIN.SCALES), size=num_images)
     assert cfg.TRAIN.BATCH_SIZE % num_images == 0, \
         'num_images ({}) must divide BATCH_SIZE ({})'.format(num_images, cfg.TRAIN.BATCH_SIZE)
     if device_blob:
-        im_blob, im_scales = _get_image_blob_device(roidb, random_scale_inds)
+        im_blob, im_scales = _get_image_blob_device(roidb, random_scale_inds, device_decode=device_decode)
     else:
         im_blob, im_scales = _get_image_blob(roidb, random_scale_inds)
     blobs = {'data': im_blob}

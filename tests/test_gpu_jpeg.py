@@ -66,3 +66,31 @@ def test_errors_are_loud(cuda):
     assert e.value.code == _lib.ERR_UNSUPPORTED
     ok = jpeg.imdecode_batch([good], cuda).cpu().numpy()[0]                         # decoder still usable afterwards
     assert np.array_equal(ok, cv2.imdecode(np.frombuffer(good, np.uint8), cv2.IMREAD_COLOR))
+
+
+def test_minibatch_device_decode_equals_imread_path(cuda, tmp_path):
+    """get_minibatch / _get_image_blob_device with device_decode=True: roidb entries name JPEG files, as in the
+    reference (roidb[i]['image'], minibatch.py:85); the blob equals the one built from cv2.imread on the host."""
+    import scipy.sparse
+    from image_denoising_b200 import minibatch
+    paths = []
+    for i, (q, s) in enumerate([(90, S420), (80, S444), (70, S420)]):
+        p = str(tmp_path / ("im%d.jpg" % i))
+        with open(p, "wb") as f:
+            f.write(encode(synth_image(375, 500, 20 + i, "smooth"), q, s))
+        paths.append(p)
+    raw = synth_image(375, 500, 30, "smooth")                                        # in-memory entry in the same shape group
+
+    def entry(im, i, spec, flipped):
+        return {'image': im, 'noise_type': spec, 'flipped': flipped, 'index': i,
+                'boxes': np.array([[10, 20, 100, 120]], np.float32), 'gt_classes': np.array([3], np.int32),
+                'gt_overlaps': scipy.sparse.csr_matrix(np.ones((1, 21), np.float32))}
+
+    roidb = [entry(paths[0], 0, "sap_median_var0.4", False), entry(paths[1], 1, "original_gaus_blur", True),
+             entry(raw, 2, "periodic_mean_var100", False), entry(paths[2], 3, "shader", True)]
+    a, sa = minibatch._get_image_blob_device(roidb, [0, 0, 0, 0])
+    b, sb = minibatch._get_image_blob_device(roidb, [0, 0, 0, 0], device_decode=True)
+    assert sa == sb and torch.equal(a, b)
+    only_files = [roidb[0], roidb[1], roidb[3]]
+    c, _ = minibatch._get_image_blob_device(only_files, [0, 0, 0], device_decode=True)
+    assert torch.equal(c, a[[0, 1, 3]])
