@@ -25,6 +25,9 @@ therefore pinned as follows:
   * the skimage / pywt restatement is "parity unpinned" against the real
     libraries (they cannot be installed: no network); it is held by property
     tests (perfect reconstruction, Parseval, BT.601 anchors, hand-computed Haar
-    cases) in tests/test_oracle_wavelet.py.
+    cases) in tests/test_oracle_wavelet.py;
+  * ``oracle/jpeg.py`` (the ``cv2.imread`` stage in front of the path) restates libjpeg's
+    baseline decoder and IS pinned: byte-identical to ``cv2.imdecode`` in tests/test_oracle_jpeg.py;
+  * tests/golden/manifest.json pins 183 oracle results by SHA-256 (tests/test_golden_cpu.py).
 """
-from . import noise, denoise, wavelet, closures  # noqa: F401
+from . import noise, denoise, wavelet, closures, jpeg  # noqa: F401
