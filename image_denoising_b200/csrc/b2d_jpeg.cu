@@ -22,6 +22,7 @@
 #include <chrono>
 #include <algorithm>
 #include <cstring>
+#include <exception>
 #include <new>
 #include <string>
 #include <thread>
@@ -562,7 +563,19 @@ void b2d_jpeg_destroy(b2d_jpeg* D) {
   delete D;
 }
 
+static int jpeg_decode_impl(b2d_jpeg* D, int n, const uint8_t* const* data, const size_t* len, uint8_t* d_out, void* cuda_stream);
+
 int b2d_jpeg_decode(b2d_jpeg* D, int n, const uint8_t* const* data, const size_t* len, uint8_t* d_out, void* cuda_stream) {
+  try {                                                        // std::thread / std::vector may throw: nothing crosses the ABI
+    return jpeg_decode_impl(D, n, data, len, d_out, cuda_stream);
+  } catch (const std::exception& e) {
+    return fail(B2D_ERR_INVALID, "b2d_jpeg_decode: %s", e.what());
+  } catch (...) {
+    return fail(B2D_ERR_INVALID, "b2d_jpeg_decode: unknown host error");
+  }
+}
+
+static int jpeg_decode_impl(b2d_jpeg* D, int n, const uint8_t* const* data, const size_t* len, uint8_t* d_out, void* cuda_stream) {
   if (!D || !data || !len || (!d_out && n > 0)) return fail(B2D_ERR_INVALID, "b2d_jpeg_decode: null argument");
   if (n < 0 || n > D->max_n) return fail(B2D_ERR_INVALID, "b2d_jpeg_decode: n=%d outside [0, %d]", n, D->max_n);
   if (n == 0) return B2D_OK;
@@ -605,8 +618,15 @@ int b2d_jpeg_decode(b2d_jpeg* D, int n, const uint8_t* const* data, const size_t
   };
   const int nt = std::min(D->threads, n);
   std::vector<std::thread> pool;
-  if (nt > 1)
-    for (int t = 0; t < nt; ++t) pool.emplace_back(work);
+  if (nt > 1) {
+    try {
+      for (int t = 0; t < nt; ++t) pool.emplace_back(work);
+    } catch (...) {                                            // thread limit: stop the ones that started, report
+      abort.store(true);
+      for (auto& t : pool) t.join();
+      return fail(B2D_ERR_INVALID, "b2d_jpeg_decode: cannot start %d host threads", nt);
+    }
+  }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
   const size_t hp = ((size_t)D->h + 15) / 16 * 16, wp = ((size_t)D->w + 15) / 16 * 16;
   const unsigned max_blocks = (unsigned)(hp * wp / 64);
