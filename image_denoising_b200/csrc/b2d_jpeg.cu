@@ -168,7 +168,8 @@ static inline unsigned be16(const uint8_t* p) { return ((unsigned)p[0] << 8) | p
 static int parse_jpeg(const uint8_t* d, size_t len, Parsed& P, std::string& msg, bool header_only) {
   if (len < 4 || d[0] != 0xFF || d[1] != 0xD8) { msg = "not a JPEG stream"; return B2D_ERR_INVALID; }
   size_t i = 2;
-  bool have_sof = false;
+  bool have_sof = false, jfif = false, adobe = false;
+  int adobe_transform = -1, orientation = 1;
   int cid[3] = {0, 0, 0};
   while (i + 4 <= len) {
     if (d[i] != 0xFF) { msg = "marker expected"; return B2D_ERR_INVALID; }
@@ -218,6 +219,29 @@ static int parse_jpeg(const uint8_t* d, size_t len, Parsed& P, std::string& msg,
       if (header_only) return B2D_OK;
     } else if (m >= 0xC2 && m <= 0xCF && m != 0xC4 && m != 0xC8 && m != 0xCC) {
       msg = "only baseline sequential Huffman JPEG (SOF0 / SOF1) is decoded"; return B2D_ERR_UNSUPPORTED;
+    } else if (m == 0xE0) {
+      if (sl >= 5 && !memcmp(seg, "JFIF", 5)) jfif = true;
+    } else if (m == 0xEE) {
+      if (sl >= 12 && !memcmp(seg, "Adobe", 5)) { adobe = true; adobe_transform = seg[11]; }
+    } else if (m == 0xE1) {
+      // EXIF orientation (TIFF tag 0x0112 in IFD0): cv2.imread rotates / mirrors the decoded image for values 2..8
+      if (sl >= 14 && !memcmp(seg, "Exif\0\0", 6)) {
+        const uint8_t* t = seg + 6;
+        const size_t tl = sl - 6;
+        const bool le = t[0] == 'I' && t[1] == 'I', be = t[0] == 'M' && t[1] == 'M';
+        auto r16 = [&](size_t o) -> unsigned { return le ? (t[o] | (t[o + 1] << 8)) : ((t[o] << 8) | t[o + 1]); };
+        auto r32 = [&](size_t o) -> size_t { return le ? ((size_t)r16(o) | ((size_t)r16(o + 2) << 16)) : (((size_t)r16(o) << 16) | r16(o + 2)); };
+        if ((le || be) && tl >= 8) {
+          const size_t ifd = r32(4);
+          if (ifd + 2 <= tl) {
+            const unsigned cnt = r16(ifd);
+            for (unsigned e = 0; e < cnt && ifd + 2 + 12 * (size_t)(e + 1) <= tl; ++e) {
+              const size_t o = ifd + 2 + 12 * (size_t)e;
+              if (r16(o) == 0x0112) orientation = (int)r16(o + 8);
+            }
+          }
+        }
+      }
     } else if (m == 0xDD) {
       if (sl < 2) { msg = "bad DRI"; return B2D_ERR_INVALID; }
       P.dri = (int)be16(seg);
@@ -230,6 +254,18 @@ static int parse_jpeg(const uint8_t* d, size_t len, Parsed& P, std::string& msg,
         if (P.td[c] > 3 || P.ta[c] > 3 || !P.dc[P.td[c]].present || !P.ac[P.ta[c]].present || !P.have_q[P.tq[c]]) {
           msg = "scan refers to a missing table"; return B2D_ERR_INVALID;
         }
+      }
+      if (orientation >= 2 && orientation <= 8) {
+        msg = "EXIF orientation " + std::to_string(orientation) + ": cv2.imread would rotate / mirror this image";
+        return B2D_ERR_UNSUPPORTED;
+      }
+      // libjpeg's colour-space guess for 3 components (jdapimin.c default_decompress_parms): RGB streams are not converted
+      if (P.ncomp == 3) {
+        bool rgb = false;
+        if (jfif) rgb = false;
+        else if (adobe) rgb = adobe_transform == 0;
+        else rgb = cid[0] == 'R' && cid[1] == 'G' && cid[2] == 'B';
+        if (rgb) { msg = "RGB-coded JPEG (Adobe transform 0 / 'RGB' component ids)"; return B2D_ERR_UNSUPPORTED; }
       }
       P.scan = i + 2 + L;
       return B2D_OK;

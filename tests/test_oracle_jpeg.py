@@ -69,3 +69,38 @@ def test_unsupported_streams_fail_loudly():
     good = encode(img, 90)
     with pytest.raises(_lib.B2DError):
         jpeg.entropy_decode(good[:len(good) // 3])           # truncated inside the headers / tables
+
+
+def _insert_after_soi(data, marker, payload):
+    import struct
+    return data[:2] + bytes([0xFF, marker]) + struct.pack(">H", len(payload) + 2) + payload + data[2:]
+
+
+def test_exif_orientation_and_rgb_streams_are_refused():
+    """cv2.imread applies the EXIF orientation (checked here against cv2 itself) and libjpeg does not colour-convert
+    RGB-coded streams: the device decoder, which does neither, must refuse such files instead of returning other bytes."""
+    import struct
+    from image_denoising_b200 import _lib, jpeg
+    img = synth_image(24, 40, 4, "smooth")
+    base = encode(img, 90)
+    tiff = b"II*\x00" + struct.pack("<I", 8) + struct.pack("<H", 1) + struct.pack("<HHII", 0x0112, 3, 1, 6) + struct.pack("<I", 0)
+    rotated = _insert_after_soi(base, 0xE1, b"Exif\x00\x00" + tiff)
+    plain = cv2.imdecode(np.frombuffer(base, np.uint8), cv2.IMREAD_COLOR)
+    turned = cv2.imdecode(np.frombuffer(rotated, np.uint8), cv2.IMREAD_COLOR)
+    assert plain.shape == (24, 40, 3) and turned.shape == (40, 24, 3)           # orientation 6: cv2 rotates
+    with pytest.raises(_lib.B2DError) as e:
+        jpeg.entropy_decode(rotated)
+    assert e.value.code == _lib.ERR_UNSUPPORTED
+    upright = _insert_after_soi(base, 0xE1, b"Exif\x00\x00" + tiff.replace(struct.pack("<HHII", 0x0112, 3, 1, 6), struct.pack("<HHII", 0x0112, 3, 1, 1)))
+    assert len(jpeg.entropy_decode(upright)) == 3                                # orientation 1 decodes
+    # Adobe APP14 with transform 0 and no JFIF segment = RGB-coded
+    assert base[2:4] == b"\xff\xe0"
+    jfif_len = struct.unpack(">H", base[4:6])[0]
+    no_jfif = base[:2] + base[4 + jfif_len:]
+    adobe = _insert_after_soi(no_jfif, 0xEE, b"Adobe\x00\x64\x00\x00\x00\x00\x00")
+    with pytest.raises(_lib.B2DError) as e:
+        jpeg.entropy_decode(adobe)
+    assert e.value.code == _lib.ERR_UNSUPPORTED
+    ycc = _insert_after_soi(no_jfif, 0xEE, b"Adobe\x00\x64\x00\x00\x00\x00\x01")
+    want = cv2.imdecode(np.frombuffer(ycc, np.uint8), cv2.IMREAD_COLOR)
+    assert np.array_equal(J.decode(ycc), want) and len(jpeg.entropy_decode(ycc)) == 3
