@@ -206,6 +206,20 @@ void b2d_jpeg_destroy(b2d_jpeg* dec);
  * that compare it with oracle/jpeg.py::entropy_decode.  blocks_x / blocks_y: 3 ints each. */
 int b2d_jpeg_entropy(const uint8_t* data, size_t len, int16_t* h_coef, size_t capacity, int* blocks_x, int* blocks_y);
 
+/* SURVEY 8(f) f4 - the reference's only native code: greedy NMS of score-sorted boxes, `_nms` of lib/nms/gpu_nms.hpp:1
+ *   (lib/nms/nms_kernel.cu:91-144; bound by lib/nms/gpu_nms.pyx:16-31, dispatched by lib/model/nms_wrapper.py:15-23).
+ *   b2d_nms has `_nms`'s exact signature and meaning: boxes_host = boxes_num x boxes_dim float32 rows
+ *   [x1, y1, x2, y2, score, ...] ALREADY sorted by descending score (gpu_nms.pyx sorts before the call); keep_out receives
+ *   the kept row positions in ascending order, *num_out their count; box j is dropped when a kept i < j has
+ *   IoU > nms_overlap_thresh ("+1" pixel convention, float32, the kernel's operation order).  Returns a status instead of
+ *   aborting (the reference's CUDA_CHECK exits the process).  The mask stays on the device and the sweep runs there.
+ *   b2d_nms_device: the same on device buffers (d_ws of b2d_nms_workspace_bytes, asynchronous on cuda_stream). */
+int b2d_nms(int* keep_out, int* num_out, const float* boxes_host, int boxes_num, int boxes_dim, float nms_overlap_thresh,
+            int device_id);
+int b2d_nms_workspace_bytes(int boxes_num, size_t* bytes);
+int b2d_nms_device(const float* d_boxes, int boxes_num, int boxes_dim, float nms_overlap_thresh, int* d_keep, int* d_num,
+                   void* d_ws, void* cuda_stream);
+
 /* Per-image result statistics gathered after the run (8(e): the only data
  * that ever crosses GPUs): checksum = sum of bytes * (1 + index mod 251)
  * mod 2^64 of d_out[i]; sse = sum (d_out - d_ref)^2 (for PSNR vs clean). */
