@@ -496,13 +496,16 @@ __global__ void __launch_bounds__(128) k_jpeg_color(const JpegImg* desc, const u
 
 using namespace b2d;
 
+static const int kJpegChunk = 16, kJpegRing = 8;   // images per upload / launch, chunks in the staging ring (128 images)
+
 struct b2d_jpeg {
-  int device, max_n, h, w, threads;
+  int device, max_n, cap, h, w, threads;     // cap = ring of staged images (pinned + device scratch), a multiple of the chunk size
   size_t coef_per_img, plane_per_img;      // int16 / bytes
   int16_t *h_coef, *d_coef;
   JpegImg *h_desc, *d_desc;
   uint8_t* d_planes;
-  cudaEvent_t uploaded;
+  cudaEvent_t chunk_ev[16];                 // upload of ring chunk k finished -> its pinned slots are free again
+  cudaEvent_t uploaded;                      // last upload of the previous call
   bool pending;
 };
 
@@ -568,16 +571,18 @@ int b2d_jpeg_create(b2d_jpeg** out, int device, int max_n, int h, int w, int hos
   if (!D) return fail(B2D_ERR_INVALID, "out of host memory");
   memset(D, 0, sizeof(*D));
   D->device = device; D->max_n = max_n; D->h = h; D->w = w;
+  D->cap = std::min((max_n + kJpegChunk - 1) / kJpegChunk, kJpegRing) * kJpegChunk;
   D->threads = host_threads > 0 ? host_threads : (int)std::max(1u, std::thread::hardware_concurrency());
   const size_t hp = ((size_t)h + 15) / 16 * 16, wp = ((size_t)w + 15) / 16 * 16;   // whole MCUs for every sampling
   D->coef_per_img = 3 * hp * wp;
   D->plane_per_img = 3 * hp * wp;
-  cudaError_t e = cudaMallocHost(&D->h_coef, D->coef_per_img * max_n * sizeof(int16_t));
-  if (e == cudaSuccess) e = cudaMallocHost(&D->h_desc, sizeof(JpegImg) * max_n);
-  if (e == cudaSuccess) e = cudaMalloc(&D->d_coef, D->coef_per_img * max_n * sizeof(int16_t));
-  if (e == cudaSuccess) e = cudaMalloc(&D->d_desc, sizeof(JpegImg) * max_n);
-  if (e == cudaSuccess) e = cudaMalloc(&D->d_planes, D->plane_per_img * max_n);
+  cudaError_t e = cudaMallocHost(&D->h_coef, D->coef_per_img * D->cap * sizeof(int16_t));
+  if (e == cudaSuccess) e = cudaMallocHost(&D->h_desc, sizeof(JpegImg) * D->cap);
+  if (e == cudaSuccess) e = cudaMalloc(&D->d_coef, D->coef_per_img * D->cap * sizeof(int16_t));
+  if (e == cudaSuccess) e = cudaMalloc(&D->d_desc, sizeof(JpegImg) * D->cap);
+  if (e == cudaSuccess) e = cudaMalloc(&D->d_planes, D->plane_per_img * D->cap);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&D->uploaded, cudaEventDisableTiming);
+  for (int k = 0; k < kJpegRing && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&D->chunk_ev[k], cudaEventDisableTiming);
   if (e != cudaSuccess) {
     b2d_jpeg_destroy(D);
     return fail_cuda(e, "b2d_jpeg_create allocations");
@@ -596,12 +601,16 @@ void b2d_jpeg_destroy(b2d_jpeg* D) {
   if (D->d_desc) cudaFree(D->d_desc);
   if (D->d_planes) cudaFree(D->d_planes);
   if (D->uploaded) cudaEventDestroy(D->uploaded);
+  for (int k = 0; k < kJpegRing; ++k)
+    if (D->chunk_ev[k]) cudaEventDestroy(D->chunk_ev[k]);
   delete D;
 }
 
 static int jpeg_decode_impl(b2d_jpeg* D, int n, const uint8_t* const* data, const size_t* len, uint8_t* d_out, void* cuda_stream);
 
 int b2d_jpeg_decode(b2d_jpeg* D, int n, const uint8_t* const* data, const size_t* len, uint8_t* d_out, void* cuda_stream) {
+  if (!D || !data || !len || (!d_out && n > 0)) return fail(B2D_ERR_INVALID, "b2d_jpeg_decode: null argument");
+  if (n < 0 || n > D->max_n) return fail(B2D_ERR_INVALID, "b2d_jpeg_decode: n=%d outside [0, %d]", n, D->max_n);
   try {                                                        // std::thread / std::vector may throw: nothing crosses the ABI
     return jpeg_decode_impl(D, n, data, len, d_out, cuda_stream);
   } catch (const std::exception& e) {
@@ -612,20 +621,21 @@ int b2d_jpeg_decode(b2d_jpeg* D, int n, const uint8_t* const* data, const size_t
 }
 
 static int jpeg_decode_impl(b2d_jpeg* D, int n, const uint8_t* const* data, const size_t* len, uint8_t* d_out, void* cuda_stream) {
-  if (!D || !data || !len || (!d_out && n > 0)) return fail(B2D_ERR_INVALID, "b2d_jpeg_decode: null argument");
-  if (n < 0 || n > D->max_n) return fail(B2D_ERR_INVALID, "b2d_jpeg_decode: n=%d outside [0, %d]", n, D->max_n);
   if (n == 0) return B2D_OK;
   CKJ(cudaSetDevice(D->device));
-  if (D->pending) { CKJ(cudaEventSynchronize(D->uploaded)); D->pending = false; }   // pinned staging is free again
-  // Host threads decode images in order; the calling thread uploads and launches chunk after chunk as soon as a
-  // chunk's images are done, so the copies and the kernels run under the Huffman decoding of the following chunks.
-  constexpr int CH = 16;
+  if (D->pending) { CKJ(cudaEventSynchronize(D->uploaded)); D->pending = false; }   // the whole pinned ring is free again
+  // Host threads decode images in order into a ring of `cap` staging slots (image i -> slot i % cap); the calling
+  // thread uploads and launches chunk after chunk as soon as a chunk's images are done and releases a chunk's slots
+  // when its upload event has fired, so copies and kernels run under the Huffman decoding of the following chunks
+  // and the pinned memory stays bounded for any batch size.
+  constexpr int CH = kJpegChunk;
+  const int cap = D->cap, ring = cap / CH;
   std::vector<int> rc(n, B2D_OK);
   std::vector<std::string> msg(n);
   std::vector<size_t> used(n, 0);
   std::vector<std::atomic<int>> done(n);
   for (auto& f : done) f.store(0, std::memory_order_relaxed);
-  std::atomic<int> next(0);
+  std::atomic<int> next(0), free_upto(0);                      // images < free_upto have left the staging ring
   std::atomic<bool> abort(false);
   auto decode_one = [&](int i, Parsed* P) {
     *P = Parsed();
@@ -638,14 +648,16 @@ static int jpeg_decode_impl(b2d_jpeg* D, int n, const uint8_t* const* data, cons
                std::to_string(D->h) + " x " + std::to_string(D->w);
       return;
     }
-    JpegImg& J = D->h_desc[i];
+    JpegImg& J = D->h_desc[i % cap];
     layout(*P, J);
     used[i] = (size_t)J.coef_off[J.ncomp - 1] + (size_t)J.bx[J.ncomp - 1] * J.by[J.ncomp - 1] * 64;
-    rc[i] = entropy_decode(data[i], len[i], *P, J, D->h_coef + (size_t)i * D->coef_per_img, msg[i]);
+    rc[i] = entropy_decode(data[i], len[i], *P, J, D->h_coef + (size_t)(i % cap) * D->coef_per_img, msg[i]);
   };
   auto work = [&]() {
     Parsed* P = new (std::nothrow) Parsed();
     for (int i = next.fetch_add(1); i < n; i = next.fetch_add(1)) {
+      while (i >= free_upto.load(std::memory_order_acquire) + cap && !abort.load(std::memory_order_relaxed))
+        std::this_thread::sleep_for(std::chrono::microseconds(20));      // slot still being uploaded
       if (!P) { rc[i] = B2D_ERR_INVALID; msg[i] = "out of host memory"; }
       else if (!abort.load(std::memory_order_relaxed)) decode_one(i, P);
       done[i].store(1, std::memory_order_release);
@@ -667,15 +679,29 @@ static int jpeg_decode_impl(b2d_jpeg* D, int n, const uint8_t* const* data, cons
   const size_t hp = ((size_t)D->h + 15) / 16 * 16, wp = ((size_t)D->w + 15) / 16 * 16;
   const unsigned max_blocks = (unsigned)(hp * wp / 64);
   Parsed* mine = nt > 1 ? nullptr : new (std::nothrow) Parsed();
-  int status = B2D_OK, bad = -1;
+  int status = B2D_OK, bad = -1, enqueued = 0, released = 0;   // chunks
   cudaError_t ce = cudaSuccess;
+  auto release = [&](bool block) {                             // publish the slots of chunks whose upload has finished
+    while (released < enqueued) {
+      const cudaError_t q = block ? cudaEventSynchronize(D->chunk_ev[released % ring]) : cudaEventQuery(D->chunk_ev[released % ring]);
+      if (q == cudaErrorNotReady) return;
+      if (q != cudaSuccess) { ce = q; return; }
+      ++released;
+      free_upto.store(std::min(n, released * CH), std::memory_order_release);
+      block = false;
+    }
+  };
   for (int first = 0; first < n && status == B2D_OK && ce == cudaSuccess; first += CH) {
     const int cnt = std::min(CH, n - first);
     size_t width = 0;
-    for (int i = first; i < first + cnt; ++i) {
+    for (int i = first; i < first + cnt && ce == cudaSuccess; ++i) {
       if (nt > 1) {
-        while (!done[i].load(std::memory_order_acquire)) std::this_thread::sleep_for(std::chrono::microseconds(30));   // not a spin: every core is decoding
+        while (!done[i].load(std::memory_order_acquire) && ce == cudaSuccess) {
+          release(false);
+          std::this_thread::sleep_for(std::chrono::microseconds(30));   // not a spin: every core is decoding
+        }
       } else if (mine) {
+        while (i >= free_upto.load(std::memory_order_relaxed) + cap && ce == cudaSuccess) release(true);
         decode_one(i, mine);
       } else {
         rc[i] = B2D_ERR_INVALID; msg[i] = "out of host memory";
@@ -683,17 +709,20 @@ static int jpeg_decode_impl(b2d_jpeg* D, int n, const uint8_t* const* data, cons
       if (rc[i] != B2D_OK && status == B2D_OK) { status = rc[i]; bad = i; }
       width = std::max(width, used[i]);
     }
-    if (status != B2D_OK) break;
+    if (status != B2D_OK || ce != cudaSuccess) break;
+    const int slot = first % cap;
     const size_t pitch = D->coef_per_img * sizeof(int16_t);
-    ce = cudaMemcpyAsync(D->d_desc + first, D->h_desc + first, sizeof(JpegImg) * cnt, cudaMemcpyHostToDevice, st);
+    ce = cudaMemcpyAsync(D->d_desc + slot, D->h_desc + slot, sizeof(JpegImg) * cnt, cudaMemcpyHostToDevice, st);
     if (ce == cudaSuccess)
-      ce = cudaMemcpy2DAsync(D->d_coef + (size_t)first * D->coef_per_img, pitch, D->h_coef + (size_t)first * D->coef_per_img, pitch,
+      ce = cudaMemcpy2DAsync(D->d_coef + (size_t)slot * D->coef_per_img, pitch, D->h_coef + (size_t)slot * D->coef_per_img, pitch,
                              width * sizeof(int16_t), cnt, cudaMemcpyHostToDevice, st);
+    if (ce == cudaSuccess) ce = cudaEventRecord(D->chunk_ev[enqueued % ring], st);
     if (ce != cudaSuccess) break;
-    k_jpeg_idct<<<dim3((max_blocks + 127) / 128, 3, cnt), 128, 0, st>>>(D->d_desc + first, D->d_coef + (size_t)first * D->coef_per_img,
-                                                                       D->d_planes + (size_t)first * D->plane_per_img,
+    ++enqueued;
+    k_jpeg_idct<<<dim3((max_blocks + 127) / 128, 3, cnt), 128, 0, st>>>(D->d_desc + slot, D->d_coef + (size_t)slot * D->coef_per_img,
+                                                                       D->d_planes + (size_t)slot * D->plane_per_img,
                                                                        D->coef_per_img, D->plane_per_img);
-    k_jpeg_color<<<dim3((D->w + 511) / 512, D->h, cnt), 128, 0, st>>>(D->d_desc + first, D->d_planes + (size_t)first * D->plane_per_img,
+    k_jpeg_color<<<dim3((D->w + 511) / 512, D->h, cnt), 128, 0, st>>>(D->d_desc + slot, D->d_planes + (size_t)slot * D->plane_per_img,
                                                                      D->plane_per_img, d_out + (size_t)first * D->h * D->w * 3, D->h, D->w);
     count_launch(); count_launch();
     ce = cudaGetLastError();
@@ -701,8 +730,10 @@ static int jpeg_decode_impl(b2d_jpeg* D, int n, const uint8_t* const* data, cons
   if (status != B2D_OK || ce != cudaSuccess) abort.store(true);
   for (auto& t : pool) t.join();
   delete mine;
-  cudaEventRecord(D->uploaded, st);                            // the pinned staging is busy until this point of the stream
-  D->pending = true;
+  if (enqueued) {                                              // the ring is busy until the last upload of this call
+    cudaEventRecord(D->uploaded, st);
+    D->pending = true;
+  }
   if (status != B2D_OK) return fail(status, "b2d_jpeg_decode: image %d: %s", bad, msg[bad].c_str());
   if (ce != cudaSuccess) return fail_cuda(ce, "b2d_jpeg_decode upload / kernels");
   return B2D_OK;

@@ -90,7 +90,25 @@ def test_minibatch_device_decode_equals_imread_path(cuda, tmp_path):
              entry(raw, 2, "periodic_mean_var100", False), entry(paths[2], 3, "shader", True)]
     a, sa = minibatch._get_image_blob_device(roidb, [0, 0, 0, 0])
     b, sb = minibatch._get_image_blob_device(roidb, [0, 0, 0, 0], device_decode=True)
-    assert sa == sb and torch.equal(a, b)
+    assert sa == sb and a.shape == b.shape
+    assert torch.equal(a, b), (int((a != b).sum()), [int((a[i] != b[i]).sum()) for i in range(len(roidb))])
     only_files = [roidb[0], roidb[1], roidb[3]]
     c, _ = minibatch._get_image_blob_device(only_files, [0, 0, 0], device_decode=True)
-    assert torch.equal(c, a[[0, 1, 3]])
+    assert torch.equal(c, a[[0, 1, 3]]), [int((c[j] != a[i]).sum()) for j, i in enumerate((0, 1, 3))]
+
+
+@pytest.mark.parametrize("threads", [0, 1, 3])
+def test_batches_larger_than_the_staging_ring(cuda, threads):
+    """The decoder stages 128 images at a time in a ring (8 chunks of 16): batches beyond that wrap around while earlier
+    chunks are still uploading; with 1 host thread the calling thread decodes inline."""
+    from image_denoising_b200 import jpeg
+    base = [encode(synth_image(48, 80, 70 + i, "smooth" if i % 3 else "uniform"), 60 + 3 * i, [S420, S444, S422][i % 3], i % 4)
+            for i in range(11)]
+    want = [cv2.imdecode(np.frombuffer(d, np.uint8), cv2.IMREAD_COLOR) for d in base]
+    n = 437
+    dec = jpeg.Decoder(n, 48, 80, cuda, host_threads=threads)
+    for rep in range(2):
+        got = dec.decode([base[(i * 7 + rep) % 11] for i in range(n)]).cpu().numpy()
+        for i in range(n):
+            assert np.array_equal(got[i], want[(i * 7 + rep) % 11]), (threads, rep, i)
+    dec.close()
