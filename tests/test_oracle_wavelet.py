@@ -87,3 +87,32 @@ def test_denoise_wavelet_reduces_noise_and_keeps_range():
         out = W.denoise_wavelet(noisy, wl, lv)
         assert out.min() >= 0 and out.max() <= 1
         assert ((out - clean) ** 2).mean() < 0.5 * ((noisy - clean) ** 2).mean()
+
+
+def test_published_pywavelets_examples():
+    """Known answers printed in the PyWavelets documentation (pywavelets.readthedocs.io: `pywt.dwt`, `pywt.idwt`,
+    `pywt.threshold`, `pywt.dwt_max_level`, signal extension modes) and the bior1.5 coefficient listing of
+    wavelets.pybytes.com - restated from those pages; they anchor sign, phase and ordering conventions that the
+    perfect-reconstruction properties above cannot see."""
+    # >>> pywt.dwt([1, 2, 3, 4, 5, 6], 'db1') -> cA [2.12132034 4.94974747 7.77817459], cD [-0.70710678 x 3]
+    x = np.array([[1., 2., 3., 4., 5., 6.]])
+    a, d = W.dwt_axis(x, "db1", 1)
+    assert np.allclose(a[0], [2.12132034, 4.94974747, 7.77817459], atol=5e-9)
+    assert np.allclose(d[0], [-0.70710678] * 3, atol=5e-9)
+    # >>> pywt.idwt(cA, cD, 'db1') -> [1. 2. 3. 4. 5. 6.]
+    assert np.allclose(W.idwt_axis(a, d, "db1", 1)[0], x[0], atol=1e-12)
+    # symmetric mode "... x2 x1 | x1 x2 ... xn | xn xn-1 ...": output length floor((n + F - 1) / 2); db2-sized check via bior1.5
+    y = np.arange(1.0, 8.0)[None]                      # n = 7, F = 10 -> 8 coefficients
+    a5, d5 = W.dwt_axis(y, "bior1.5", 1)
+    assert a5.shape == (1, 8) and d5.shape == (1, 8)
+    # >>> pywt.threshold(np.linspace(1, 4, 7), 2, 'soft') -> [0. 0. 0. 0.5 1. 1.5 2.]
+    assert np.allclose(W.soft_threshold(np.linspace(1, 4, 7), 2), [0, 0, 0, 0.5, 1, 1.5, 2])
+    # >>> pywt.dwt_max_level(data_len=1000, filter_len=10) -> 6   (the sym5 example: dec_len 10, as bior1.5)
+    assert W.dwt_max_level(1000, 10) == 6
+    # bior1.5 decomposition low-pass as listed: 0.0165728..., -0.0165728..., -0.1215339..., 0.1215339..., 0.7071..., ...
+    lo = W.WAVELETS["bior1.5"][0]
+    assert np.allclose(lo, [0.01657281518405971, -0.01657281518405971, -0.12153397801643787, 0.12153397801643787,
+                            0.7071067811865476, 0.7071067811865476, 0.12153397801643787, -0.12153397801643787,
+                            -0.01657281518405971, 0.01657281518405971], atol=0)
+    hi = W.WAVELETS["bior1.5"][1]
+    assert hi[4] == -0.7071067811865476 and hi[5] == 0.7071067811865476 and not any(hi[:4]) and not any(hi[6:])
