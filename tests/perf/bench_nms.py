@@ -1,12 +1,12 @@
 """b2d_nms at the reference's sizes: per-class test-time NMS (N <= 300, lib/model/test.py:1860) and RPN
 proposal NMS (N = 6000 / 12000, lib/layer_utils/proposal_layer.py:46), against the NumPy oracle on one host core.
-  python scripts/bench_nms.py"""
+  python tests/perf/bench_nms.py"""
 import json
 import os
 import sys
 import time
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 import numpy as np  # noqa: E402

@@ -6,7 +6,7 @@ stages either side of the path), against the reference's chain on one host core:
   here (one call per batch):
       file bytes -> b2d_jpeg_decode -> b2d_run(spec) -> b2d_blob_prep -> (N, H', W', 3) float32 on the GPU
 
-  python scripts/bench_pipeline.py [--n 256 --batch 64 --spec gaussian_median_var1.0 ...]"""
+  python tests/perf/bench_pipeline.py [--n 256 --batch 64 --spec gaussian_median_var1.0 ...]"""
 import argparse
 import json
 import os
@@ -14,7 +14,7 @@ import sys
 import tempfile
 import time
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 import cv2  # noqa: E402
