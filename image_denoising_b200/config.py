@@ -9,5 +9,5 @@ cfg = SimpleNamespace(
     PIXEL_MEANS=np.array([[[102.9801, 115.9465, 122.7717]]]),     # config.py:252
     RNG_SEED=3,                                                     # config.py:255
     TRAIN=SimpleNamespace(SCALES=(600,), MAX_SIZE=1000, IMS_PER_BATCH=1, BATCH_SIZE=128, USE_ALL_GT=True),
-    TEST=SimpleNamespace(SCALES=(600,), MAX_SIZE=1000),
+    TEST=SimpleNamespace(SCALES=(600,), MAX_SIZE=1000, NMS=0.3),    # config.py:160,169,176
 )

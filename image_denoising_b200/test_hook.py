@@ -60,3 +60,20 @@ def get_test_blob_device(batch):
             prep_blob_device(batch, cfg.PIXEL_MEANS, target, cfg.TEST.MAX_SIZE, out=tmp)
             blob[:, k] = tmp
     return blob.view(n * ns, hmax, wmax, 3), np.array([s[0] for s in shapes])
+
+
+def corrupt_paths_for_test_device(paths, noise, first_index=0, **overrides):
+    """The first three lines of the test loop for a batch of same-sized JPEG files, everything on the GPU:
+    `cv2.imread` (test.py:191) = `b2d_jpeg_decode` (bit-exact), closures (test.py:193-1831) = `b2d_run`.
+    Returns the (N, H, W, 3) uint8 CUDA tensor `im_detect` would get image by image (feed `get_test_blob_device`)."""
+    from . import jpeg
+    from .spec import resolve_mix
+    batch = jpeg.imread_batch(paths)
+    specs = [resolve_mix(noise, "test", None) for _ in paths]
+    return api.apply(batch, specs, seed=cfg.RNG_SEED, first_index=first_index, **overrides)
+
+
+def nms_for_test(cls_dets, thresh=None):
+    """`keep = nms(cls_dets, cfg.TEST.NMS)` of the per-class loop, test.py:1854-1862 (`b2d_nms`)."""
+    from .nms import nms
+    return nms(np.ascontiguousarray(cls_dets, dtype=np.float32), cfg.TEST.NMS if thresh is None else thresh)

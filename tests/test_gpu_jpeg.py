@@ -112,3 +112,21 @@ def test_batches_larger_than_the_staging_ring(cuda, threads):
         for i in range(n):
             assert np.array_equal(got[i], want[(i * 7 + rep) % 11]), (threads, rep, i)
     dec.close()
+
+
+def test_test_side_chain_on_device(cuda, tmp_path):
+    """test_hook.corrupt_paths_for_test_device = [corrupt_for_test(cv2.imread(p), noise, i) for p in paths] (test.py:191-1831)."""
+    from image_denoising_b200 import test_hook
+    paths = []
+    for i in range(5):
+        p = str(tmp_path / ("t%d.jpg" % i))
+        with open(p, "wb") as f:
+            f.write(encode(synth_image(96, 128, 40 + i, "smooth"), 88, S420))
+        paths.append(p)
+    for noise in ("periodic_median_var100", "shader", "sap_mean_var0.4"):
+        dev = test_hook.corrupt_paths_for_test_device(paths, noise, first_index=7).cpu().numpy()
+        for i, p in enumerate(paths):
+            want = test_hook.corrupt_for_test(cv2.imread(p), noise, 7 + i)
+            assert np.array_equal(dev[i], want), (noise, i)
+    dets = np.array([[0, 0, 9, 9, 0.9], [0, 0, 9, 9, 0.8], [5, 0, 14, 9, 0.7], [100, 100, 109, 109, 0.6]], np.float32)
+    assert [int(k) for k in test_hook.nms_for_test(dets)] == [0, 3]               # cfg.TEST.NMS = 0.3
