@@ -29,6 +29,6 @@ therefore pinned as follows:
   * ``oracle/jpeg.py`` (the ``cv2.imread`` stage in front of the path) restates libjpeg's
     baseline decoder and IS pinned: byte-identical to ``cv2.imdecode`` in tests/test_oracle_jpeg.py;
   * ``oracle/nms.py`` (SURVEY 8(f) f4) is pinned by golden vectors of the reference's lib/nms/py_cpu_nms.py;
-  * tests/golden/manifest.json pins 183 oracle results by SHA-256 (tests/test_golden_cpu.py).
+  * tests/golden/manifest.json pins 267 oracle results by SHA-256 (tests/test_golden_cpu.py).
 """
 from . import noise, denoise, wavelet, closures, jpeg, nms  # noqa: F401

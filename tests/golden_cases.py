@@ -21,6 +21,8 @@ NATURAL = os.path.join(GOLDEN, "natural_120x160.npz")
 
 LEVEL_MID = {"gaussian": "1.0", "speckle": "1.0", "sap": "0.4", "uniform": "0.6", "gamma": "0.1", "rayleigh": "0.2",
              "brownian": "0.09"}
+OTHER_LEVELS = {"gaussian": ["0.1", "1.5"], "speckle": ["0.5", "2.0"], "sap": ["0.2", "0.8"], "uniform": ["0.2", "1.2"],
+                "gamma": ["0.05", "0.2"], "rayleigh": ["0.1", "0.3"], "brownian": ["0.9", "0.009"]}
 # tolerance class per branch (BASELINE.json north_star): "exact" = digest must match
 FLOAT_DENOISERS = ("bilateral", "wavelet")
 
@@ -49,6 +51,10 @@ def stochastic_specs():
             if noise == "brownian" and den in ("_bilateral", "_wavelet"):
                 continue
             specs.append("%s%s_var%s" % (noise, den, lvl))
+    # the other two levels of every `'var<L>' in spec` ladder (minibatch.py:98-199 and twins), noise only and + median
+    for noise, levels in OTHER_LEVELS.items():
+        for lvl in levels:
+            specs += ["%s_var%s" % (noise, lvl), "%s_median_var%s" % (noise, lvl)]
     specs += ["poisson", "poisson_median", "poisson_mean", "poisson_wavelet"]
     specs += ["quant_var3", "quant_median_var7", "quant_mean_var10"]
     return specs
@@ -62,9 +68,9 @@ def noise_of(spec):
 def draw_fields(spec, img, rng):
     """The draws of one closure call, same NumPy / SciPy calls and order as the reference
     (e.g. lib/roi_data_layer/minibatch.py:91, 259, 676, 822, 1216, 1356)."""
-    noise = noise_of(spec)
+    from oracle import closures as C
+    noise, _, level = C.ladder(spec)
     shape = img.shape
-    level = LEVEL_MID.get(noise)
     if noise in ("gaussian", "speckle"):
         return {"n": rng.normal(0.0, float(level) ** 0.5, shape)}
     if noise == "sap":

@@ -67,4 +67,4 @@ def test_cuda_path_matches_golden_manifest(cuda):
             assert (d != 0).mean() <= 1e-5, (cid, int((d != 0).sum()))
         n_tol += 1
     assert not failures, failures
-    assert n_exact >= 100 and n_tol >= 60
+    assert n_exact >= 170 and n_tol >= 90
