@@ -68,7 +68,8 @@ __global__ void __launch_bounds__(FT_THREADS, 4) k_fused3(ImageSet s, NoiseArgs 
     if (v0) {
 #pragma unroll FT_UNROLL
       for (int tr = r0; tr < rows; tr += 4) {
-        const int ys = border_map(y0 - 1 + tr, s.h, F::BORDER);
+        int ys = y0 - 1 + tr;                             // only the first / last tile row can leave the image
+        if (ys < 0 || ys >= s.h) ys = border_map(ys, s.h, F::BORDER);   // (warp-uniform: a warp shares tr)
         const uint32_t e = (uint32_t)ys * (uint32_t)s.rowbytes + (uint32_t)c;
         const uint2 a = __ldg(reinterpret_cast<const uint2*>(img + e));
         uint2 b = make_uint2(0u, 0u);
