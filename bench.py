@@ -31,7 +31,7 @@ N_IMAGES, H, W = 512, 600, 1000
 SEED = 3                                   # cfg.RNG_SEED (lib/model/config.py:255)
 ALGO_BYTES_PER_PIXEL = 6.0                 # 3 B read + 3 B written
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the two fused kernels at this workload,
-# from the `ncu --set full` capture profiles/r01c_fused3_full_raw.csv (algorithmic: 1843.2 MB)
+# from the `ncu --set full` capture profiles/r01h_fused3_full_raw.csv (same figures as r01c) (algorithmic: 1843.2 MB)
 NCU_TRAFFIC_BYTES = {"sap_mean_var0.4": 921726464 + 874275584, "gaussian_gaus_blur_var1.5": 921651456 + 875534336}
 WORKLOAD = "C2: 512x600x1000 RGB uint8 per GPU; step = sap_mean_var0.4 + gaussian_gaus_blur_var1.5"
 
@@ -310,7 +310,7 @@ def run_b200(args):
                     "d2h_bytes_per_step": len(SPECS) * nbytes, "api": "b2d_run_host (pinned host buffers)"},
             "roofline": {"bound": "hbm", "kernel": "k_fused3<%s>" % SPECS[dom], "achieved": achieved,
                          "peak": peak_gbs, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak_gbs,
-                         "traffic": NCU_TRAFFIC_BYTES.get(SPECS[dom]), "traffic_source": "profiles/r01c_fused3_full_raw.csv",
+                         "traffic": NCU_TRAFFIC_BYTES.get(SPECS[dom]), "traffic_source": "profiles/r01h_fused3_full_raw.csv",
                          "algorithmic_bytes": mpix_batch * 1e6 * ALGO_BYTES_PER_PIXEL},
             "cpu_baseline": cpu}
     print(json.dumps(line))
