@@ -32,7 +32,7 @@ SEED = 3                                   # cfg.RNG_SEED (lib/model/config.py:2
 ALGO_BYTES_PER_PIXEL = 6.0                 # 3 B read + 3 B written
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the two fused kernels at this workload,
 # from the `ncu --set full` capture profiles/r01h_fused3_full_raw.csv (same figures as r01c) (algorithmic: 1843.2 MB)
-NCU_TRAFFIC_BYTES = {"sap_mean_var0.4": 921726464 + 874275584, "gaussian_gaus_blur_var1.5": 921651456 + 875534336}
+NCU_TRAFFIC_BYTES = {"sap_mean_var0.4": 921654016 + 875183104, "gaussian_gaus_blur_var1.5": 921668352 + 874184704}
 WORKLOAD = "C2: 512x600x1000 RGB uint8 per GPU; step = sap_mean_var0.4 + gaussian_gaus_blur_var1.5"
 
 
