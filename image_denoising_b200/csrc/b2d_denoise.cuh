@@ -12,7 +12,9 @@ size_t denoise_workspace_bytes(const b2d_plan& p);
 size_t wavelet_workspace_bytes(const b2d_plan& p);
 
 // 3x3 filters for images whose row size is not a multiple of 4 bytes (W % 4 != 0)
-cudaError_t launch_filter3_bytes(int filter, const ImageSet& s, cudaStream_t st);
+cudaError_t launch_filter3_bytes(int filter, const ImageSet& s, cudaStream_t st);   // one thread per byte
+// the same through re-aligning shared-memory tiles (b2d_filter3_any.cu): the path that runs
+cudaError_t launch_filter3_any(int filter, const ImageSet& s, cudaStream_t st);
 
 }  // namespace b2d
 

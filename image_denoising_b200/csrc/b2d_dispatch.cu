@@ -59,7 +59,7 @@ int denoise_u8(const RunCtx& c, const b2d_spec& sp, const ImageSet& s) {
     NoiseArgs none{};
     none.elems = c.p->elems;
     if (word_aligned(c.p, s.in, s.out)) CK(launch_fused3(NK_NONE, f3, s, none, c.st));
-    else CK(launch_filter3_bytes(f3, s, c.st));
+    else CK(launch_filter3_any(f3, s, c.st));
     return B2D_OK;
   }
   return run_denoise_pass(*c.p, sp, s, c.ws, c.st);

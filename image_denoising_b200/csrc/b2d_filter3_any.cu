@@ -1,0 +1,220 @@
+// b2d_filter3_any.cu - the 3x3 denoisers for images whose rows are NOT word aligned
+// (W % 4 != 0, e.g. 499 or 333 pixels wide: rowbytes = 3 W is odd or 2 (mod 4)).
+//
+// Replaces cv2.GaussianBlur(im, (3, 3), 0) / cv2.blur(im, (3, 3)) / cv2.medianBlur(im, 3) of
+// lib/roi_data_layer/minibatch.py:117-170 for those widths.  The first version of this path
+// (b2d_filter3_bytes.cu) ran one thread per output byte, 9 byte loads each: 27x slower per pixel
+// than the aligned tile kernel.  Here the rows are RE-ALIGNED on the way into shared memory, so the
+// filter phase is the packed-lane code of the hot kernel (b2d_filter3w.cuh) unchanged:
+//
+//   load   : every row of the tile starts at an arbitrary byte address; a thread reads the two
+//            aligned words that straddle its 4 bytes and funnel-shifts them by the row's phase
+//            (address & 3).  8 rows per step, so 16 loads per thread are in flight.
+//   filter : as k_fused3 (bands, KW words per thread), results into a second shared tile.
+//   store  : the mirror image - words that lie completely inside the row are rebuilt with a
+//            funnel shift from the result tile and written as aligned 32-bit stores, the 0-3
+//            bytes at either end of the row segment as byte stores.
+// Algorithmic HBM traffic: 3 B read + 3 B written per pixel.
+#include "b2d_denoise.cuh"
+#include "b2d_filter3w.cuh"
+
+#include <cstdlib>
+
+namespace b2d {
+
+constexpr int FA_THREADS = 256;
+constexpr int FA_TWB = 1024;               // tile width in bytes (one word per thread and row)
+constexpr int FA_TH = 32;                  // tile height in rows
+constexpr int FA_APRON = 16;               // shared bytes left of the tile (8 are loaded, 3 are used)
+constexpr int FA_SROW = FA_TWB + 32;
+constexpr int FA_ROWS = FA_TH + 2;
+constexpr int FA_XW = 3;                   // words per row past the first 256: [c0 - 8, c0 + 1028) is loaded
+constexpr size_t FA_SMEM = (size_t)FA_ROWS * FA_SROW + (size_t)FA_TH * FA_TWB;
+
+// the aligned word at p, bytes outside [lo, hi) read as 0
+__device__ __forceinline__ uint32_t guarded_word(const uint8_t* p, const uint8_t* lo, const uint8_t* hi) {
+  if (p >= lo && p + 4 <= hi) return __ldg(reinterpret_cast<const uint32_t*>(p));
+  uint32_t v = 0u;
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    if (p + i >= lo && p + i < hi) v |= (uint32_t)__ldg(p + i) << (8 * i);
+  return v;
+}
+
+template <int FILTER, int KW>
+__global__ void __launch_bounds__(FA_THREADS, 3) k_filter3_tile_any(ImageSet s) {
+  using F = Filter3W<FILTER, KW>;
+  constexpr int TPB = FA_TWB / (4 * KW);            // threads per band
+  constexpr int BANDS = FA_THREADS / TPB;
+  constexpr int BAND_H = FA_TH / BANDS;
+  extern __shared__ __align__(16) uint8_t smem[];
+  uint8_t* s_out = smem + FA_ROWS * FA_SROW;
+
+  const int tid = threadIdx.x;
+  const int c0 = blockIdx.x * FA_TWB;               // first byte column of the tile
+  const int y0 = blockIdx.y * FA_TH;
+  const int img_local = image_of(s, blockIdx.z);
+  const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
+  const uint8_t* img_end = img + s.elems;
+  const int rows = min(FA_ROWS, s.h - y0 + 2);      // tile row tr holds image row y0 - 1 + tr
+
+  // ---- load: bytes [c0 - 8, c0 + 1028) of every tile row, re-aligned to the shared row ----
+  auto row_src = [&](int tr) {
+    int ys = y0 - 1 + tr;
+    if (ys < 0 || ys >= s.h) ys = border_map(ys, s.h, F::BORDER);
+    return img + (int64_t)ys * s.rowbytes + c0 - 8;                          // lands at shared offset APRON - 8
+  };
+  auto fetch = [&](const uint8_t* src, int j) {
+    const unsigned phase = (unsigned)(reinterpret_cast<uintptr_t>(src) & 3u);
+    const uint8_t* p = src - phase + 4 * j;
+    uint32_t a, b = 0u;
+    if (p >= img && p + 8 <= img_end) {                                       // both words inside the image
+      a = __ldg(reinterpret_cast<const uint32_t*>(p));
+      if (phase) b = __ldg(reinterpret_cast<const uint32_t*>(p + 4));
+    } else {
+      a = guarded_word(p, img, img_end);
+      if (phase) b = guarded_word(p + 4, img, img_end);
+    }
+    return phase ? __funnelshift_r(a, b, 8 * phase) : a;
+  };
+#pragma unroll 1
+  for (int tr0 = 0; tr0 < rows; tr0 += 8) {
+    uint32_t v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      if (tr0 + u < rows) v[u] = fetch(row_src(tr0 + u), tid);
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      if (tr0 + u < rows)
+        *reinterpret_cast<uint32_t*>(smem + (tr0 + u) * FA_SROW + FA_APRON - 8 + 4 * tid) = v[u];
+  }
+  for (int it = tid; it < FA_XW * rows; it += FA_THREADS) {                  // the words past the first 256 of a row
+    const int tr = it / FA_XW, j = FA_TWB / 4 + (it - FA_XW * tr);
+    *reinterpret_cast<uint32_t*>(smem + tr * FA_SROW + FA_APRON - 8 + 4 * j) = fetch(row_src(tr), j);
+  }
+  __syncthreads();
+
+  // ---- left / right image border: one apron pixel.  The row may end 1-3 bytes into the NEXT
+  // tile (then this tile still needs the border pixel behind it) or 1-3 bytes into THIS one
+  // (then its source pixel lies left of c0: that is why the load starts at c0 - 8). ----
+  const bool left_edge = (c0 == 0);
+  const bool right_edge = (s.rowbytes <= c0 + FA_TWB + 3);
+  if (left_edge || right_edge) {
+    if (tid < rows) {
+      uint8_t* srow = smem + tid * FA_SROW + FA_APRON - c0;
+      if (left_edge) {
+        const int sp3 = 3 * border_map(-1, s.w, F::BORDER);
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) srow[ch - 3] = srow[sp3 + ch];
+      }
+      if (right_edge) {
+        const int sp3 = 3 * border_map(s.w, s.w, F::BORDER);
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) srow[s.rowbytes + ch] = srow[sp3 + ch];
+      }
+    }
+    __syncthreads();
+  }
+
+  // ---- filter: a thread owns KW words of one band and slides down it ------------------
+  {
+    const int band = tid / TPB, q = tid - band * TPB;
+    const int c = c0 + 4 * KW * q;
+    const int o0 = band * BAND_H;
+    const int nrows = min(BAND_H, s.h - y0 - o0);
+    if (c < s.rowbytes && nrows > 0) {
+      const uint8_t* sp = smem + FA_APRON + 4 * KW * q + o0 * FA_SROW;
+      auto load_row = [&](int tr, typename F::Part& p) {
+        const uint8_t* rp = sp + tr * FA_SROW;
+        uint32_t w[KW + 2];
+        w[0] = *reinterpret_cast<const uint32_t*>(rp - 4);
+        if (KW == 4) {
+          const uint4 v = *reinterpret_cast<const uint4*>(rp);
+          w[1] = v.x; w[2] = v.y; w[3] = v.z; w[KW] = v.w;
+        } else {
+          const uint2 v = *reinterpret_cast<const uint2*>(rp);
+          w[1] = v.x; w[KW] = v.y;
+        }
+        w[KW + 1] = *reinterpret_cast<const uint32_t*>(rp + 4 * KW);
+        RowLanes<KW> rl;
+        rl.split(w);
+        F::hpart(rl, p);
+      };
+      typename F::Part p0, p1, p2;
+      load_row(0, p0);
+      load_row(1, p1);
+      uint8_t* optr = s_out + o0 * FA_TWB + 4 * KW * q;
+#pragma unroll
+      for (int r = 0; r < BAND_H; ++r) {
+        if (r >= nrows) break;
+        typename F::Part& pt = (r % 3 == 0) ? p0 : (r % 3 == 1) ? p1 : p2;
+        typename F::Part& pm = (r % 3 == 0) ? p1 : (r % 3 == 1) ? p2 : p0;
+        typename F::Part& pb = (r % 3 == 0) ? p2 : (r % 3 == 1) ? p0 : p1;
+        load_row(r + 2, pb);
+        uint32_t o[KW];
+        F::vcomb(pt, pm, pb, o);
+        if (KW == 4) *reinterpret_cast<uint4*>(optr) = make_uint4(o[0], o[1], o[KW - 2], o[KW - 1]);
+        else *reinterpret_cast<uint2*>(optr) = make_uint2(o[0], o[1]);
+        optr += FA_TWB;
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- store: aligned words of the destination row segment, byte stores at its two ends ----
+  const int out_rows = min(FA_TH, s.h - y0);
+  const int len = min(FA_TWB, s.rowbytes - c0);     // bytes of a row that belong to this tile
+  uint8_t* out_img = s.out + (uint64_t)img_local * s.elems;
+  auto put = [&](int r, int k) {                    // destination word k of tile row r
+    uint8_t* dst = out_img + (uint64_t)(y0 + r) * s.rowbytes + c0;
+    const int po = (int)(reinterpret_cast<uintptr_t>(dst) & 3u);
+    const int b0 = 4 * k - po;                      // first tile byte of the word
+    if (b0 >= len || b0 + 4 <= 0) return;
+    const uint8_t* srow = s_out + r * FA_TWB;
+    if (b0 >= 0 && b0 + 4 <= len) {
+      const uint32_t* sw = reinterpret_cast<const uint32_t*>(srow);
+      const uint32_t v = po ? __funnelshift_r(sw[k - 1], sw[k], 8 * (4 - po)) : sw[k];
+      *reinterpret_cast<uint32_t*>(dst + b0) = v;
+    } else {
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        if (b0 + i >= 0 && b0 + i < len) dst[b0 + i] = srow[b0 + i];
+    }
+  };
+#pragma unroll 4
+  for (int r = 0; r < out_rows; ++r) put(r, tid);
+  if (tid < out_rows) put(tid, FA_THREADS);         // word 256 exists when the segment starts off a word boundary
+}
+
+template <int FILTER>
+static cudaError_t launch_tile_any(const ImageSet& s, cudaStream_t st) {
+  constexpr int KW = FILTER == FK_MEDIAN3 ? 2 : 4;
+  static bool attr_done[64] = {};               // per device: the attribute lives in the context
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_done[dev & 63]) {
+    const cudaError_t e = cudaFuncSetAttribute(k_filter3_tile_any<FILTER, KW>,
+                                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FA_SMEM);
+    if (e != cudaSuccess) return e;
+    attr_done[dev & 63] = true;
+  }
+  const dim3 grid((s.rowbytes + FA_TWB - 1) / FA_TWB, (s.h + FA_TH - 1) / FA_TH, s.count);
+  k_filter3_tile_any<FILTER, KW><<<grid, FA_THREADS, FA_SMEM, st>>>(s);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_filter3_any(int filter, const ImageSet& s, cudaStream_t st) {
+  if (s.count <= 0) return cudaSuccess;
+  // B2D_FILTER_BYTES=1 forces the one-thread-per-byte kernel (the cross-check of the two in the tests)
+  static const char* bytes_env = getenv("B2D_FILTER_BYTES");
+  if ((bytes_env && bytes_env[0] == '1') || s.elems >= (1ull << 31)) return launch_filter3_bytes(filter, s, st);
+  switch (filter) {
+    case FK_GAUS3: return launch_tile_any<FK_GAUS3>(s, st);
+    case FK_MEAN3: return launch_tile_any<FK_MEAN3>(s, st);
+    case FK_MEDIAN3: return launch_tile_any<FK_MEDIAN3>(s, st);
+  }
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace b2d
