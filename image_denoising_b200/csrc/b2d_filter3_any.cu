@@ -7,9 +7,9 @@
 // than the aligned tile kernel.  Here the rows are RE-ALIGNED on the way into shared memory, so the
 // filter phase is the packed-lane code of the hot kernel (b2d_filter3w.cuh) unchanged:
 //
-//   load   : every row of the tile starts at an arbitrary byte address; a thread reads the two
-//            aligned words that straddle its 4 bytes and funnel-shifts them by the row's phase
-//            (address & 3).  8 rows per step, so 16 loads per thread are in flight.
+//   load   : every row of the tile starts at an arbitrary byte address; a warp takes a row, a lane
+//            reads the two aligned words that straddle its 4 bytes and funnel-shifts them by the
+//            row's phase (address & 3); 9 words per lane and row, 18 loads in flight.
 //   filter : as k_fused3 (bands, KW words per thread), results into a second shared tile.
 //   store  : the mirror image - words that lie completely inside the row are rebuilt with a
 //            funnel shift from the result tile and written as aligned 32-bit stores, the 0-3
@@ -64,33 +64,40 @@ __global__ void __launch_bounds__(FA_THREADS, 3) k_filter3_tile_any(ImageSet s) 
     if (ys < 0 || ys >= s.h) ys = border_map(ys, s.h, F::BORDER);
     return img + (int64_t)ys * s.rowbytes + c0 - 8;                          // lands at shared offset APRON - 8
   };
-  auto fetch = [&](const uint8_t* src, int j) {
-    const unsigned phase = (unsigned)(reinterpret_cast<uintptr_t>(src) & 3u);
-    const uint8_t* p = src - phase + 4 * j;
-    uint32_t a, b = 0u;
-    if (p >= img && p + 8 <= img_end) {                                       // both words inside the image
-      a = __ldg(reinterpret_cast<const uint32_t*>(p));
-      if (phase) b = __ldg(reinterpret_cast<const uint32_t*>(p + 4));
-    } else {
-      a = guarded_word(p, img, img_end);
-      if (phase) b = guarded_word(p + 4, img, img_end);
-    }
-    return phase ? __funnelshift_r(a, b, 8 * phase) : a;
-  };
+  // A WARP owns a tile row (rows warp, warp + 8, ...): address, phase and the in-image test are
+  // computed once per row, a lane then moves words lane, lane + 32, ... (one word per thread and
+  // row, as in the first version, cost ~25 instructions of addressing per word).
+  constexpr int NW = FA_TWB / 4 + FA_XW;            // words per tile row
+  const int warp = tid >> 5, lane = tid & 31;
 #pragma unroll 1
-  for (int tr0 = 0; tr0 < rows; tr0 += 8) {
-    uint32_t v[8];
+  for (int tr = warp; tr < rows; tr += FA_THREADS / 32) {
+    const uint8_t* src = row_src(tr);
+    const unsigned phase = (unsigned)(reinterpret_cast<uintptr_t>(src) & 3u);
+    const uint8_t* base = src - phase;              // aligned; word j of the row is funnel(base[j], base[j + 1])
+    uint32_t* sdst = reinterpret_cast<uint32_t*>(smem + tr * FA_SROW + FA_APRON - 8);
+    const uint32_t* wsrc = reinterpret_cast<const uint32_t*>(base);
+    if (base >= img && base + 4 * (NW + 1) <= img_end) {
+      if (phase) {
+        const unsigned sh = 8u * phase;
 #pragma unroll
-    for (int u = 0; u < 8; ++u)
-      if (tr0 + u < rows) v[u] = fetch(row_src(tr0 + u), tid);
+        for (int i = 0; i < (NW + 31) / 32; ++i) {
+          const int j = lane + 32 * i;
+          if (j < NW) sdst[j] = __funnelshift_r(__ldg(wsrc + j), __ldg(wsrc + j + 1), sh);
+        }
+      } else {
 #pragma unroll
-    for (int u = 0; u < 8; ++u)
-      if (tr0 + u < rows)
-        *reinterpret_cast<uint32_t*>(smem + (tr0 + u) * FA_SROW + FA_APRON - 8 + 4 * tid) = v[u];
-  }
-  for (int it = tid; it < FA_XW * rows; it += FA_THREADS) {                  // the words past the first 256 of a row
-    const int tr = it / FA_XW, j = FA_TWB / 4 + (it - FA_XW * tr);
-    *reinterpret_cast<uint32_t*>(smem + tr * FA_SROW + FA_APRON - 8 + 4 * j) = fetch(row_src(tr), j);
+        for (int i = 0; i < (NW + 31) / 32; ++i) {
+          const int j = lane + 32 * i;
+          if (j < NW) sdst[j] = __ldg(wsrc + j);
+        }
+      }
+    } else {                                        // first / last rows of an image: bytes outside it read as 0
+      for (int j = lane; j < NW; j += 32) {
+        const uint32_t a = guarded_word(base + 4 * j, img, img_end);
+        const uint32_t b2 = phase ? guarded_word(base + 4 * j + 4, img, img_end) : 0u;
+        sdst[j] = phase ? __funnelshift_r(a, b2, 8 * phase) : a;
+      }
+    }
   }
   __syncthreads();
 
@@ -165,25 +172,33 @@ __global__ void __launch_bounds__(FA_THREADS, 3) k_filter3_tile_any(ImageSet s) 
   const int out_rows = min(FA_TH, s.h - y0);
   const int len = min(FA_TWB, s.rowbytes - c0);     // bytes of a row that belong to this tile
   uint8_t* out_img = s.out + (uint64_t)img_local * s.elems;
-  auto put = [&](int r, int k) {                    // destination word k of tile row r
+#pragma unroll 1
+  for (int r = warp; r < out_rows; r += FA_THREADS / 32) {      // a warp owns a row here as well
     uint8_t* dst = out_img + (uint64_t)(y0 + r) * s.rowbytes + c0;
     const int po = (int)(reinterpret_cast<uintptr_t>(dst) & 3u);
-    const int b0 = 4 * k - po;                      // first tile byte of the word
-    if (b0 >= len || b0 + 4 <= 0) return;
+    const int head = min((4 - po) & 3, len);        // bytes in front of the first aligned word
+    const int nfull = (len - head) >> 2;            // aligned words that lie completely inside the segment
+    const int t0 = head + 4 * nfull, tail = len - t0;
     const uint8_t* srow = s_out + r * FA_TWB;
-    if (b0 >= 0 && b0 + 4 <= len) {
-      const uint32_t* sw = reinterpret_cast<const uint32_t*>(srow);
-      const uint32_t v = po ? __funnelshift_r(sw[k - 1], sw[k], 8 * (4 - po)) : sw[k];
-      *reinterpret_cast<uint32_t*>(dst + b0) = v;
+    const uint32_t* sw = reinterpret_cast<const uint32_t*>(srow);
+    uint32_t* dw = reinterpret_cast<uint32_t*>(dst + head);
+    if (head) {                                     // (nfull > 0 implies head == (4 - po) & 3; sw[m + 1] <= sw[255])
+      const unsigned sh = 8u * (unsigned)head;
+#pragma unroll
+      for (int i = 0; i < FA_TWB / 128; ++i) {
+        const int m = lane + 32 * i;
+        if (m < nfull) dw[m] = __funnelshift_r(sw[m], sw[m + 1], sh);
+      }
     } else {
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
-        if (b0 + i >= 0 && b0 + i < len) dst[b0 + i] = srow[b0 + i];
+      for (int i = 0; i < FA_TWB / 128; ++i) {
+        const int m = lane + 32 * i;
+        if (m < nfull) dw[m] = sw[m];
+      }
     }
-  };
-#pragma unroll 4
-  for (int r = 0; r < out_rows; ++r) put(r, tid);
-  if (tid < out_rows) put(tid, FA_THREADS);         // word 256 exists when the segment starts off a word boundary
+    if (lane < head) dst[lane] = srow[lane];
+    if (lane >= 4 && lane - 4 < tail) dst[t0 + lane - 4] = srow[t0 + lane - 4];
+  }
 }
 
 template <int FILTER>
