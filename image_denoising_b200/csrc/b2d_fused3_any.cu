@@ -11,31 +11,22 @@
 // Tile: TILE_H rows x TILE_WB bytes of one image per CTA.  Prologue: the
 // noised uint8 values of the tile + 1-row / 8-byte apron are generated
 // straight into shared memory (Philox is counter based, so apron values equal
-// what the neighbouring CTA generates).  Main loop: each thread owns a 4-byte
-// column word and slides down the tile keeping two row-parts in registers.
+// what the neighbouring CTA generates).  Main loop: the packed band filter of the
+// hot kernel (KW words per thread, two row-parts in registers).
 // Algorithmic HBM traffic: 3 B read + 3 B written per pixel.
 #include "b2d_kernels.cuh"
+#include "b2d_filter3w.cuh"
 
 namespace b2d {
 
 constexpr int F3_THREADS = 256;
-constexpr int F3_TILE_WB = F3_THREADS * 4;       // 1024 bytes wide
-constexpr int F3_TILE_H = 32;
-constexpr int F3_APRON = 8;                       // bytes each side (one noise group)
+constexpr int F3_TILE_WB = 1024;                  // tile width in bytes
+constexpr int F3_TILE_H = 48;                     // as the hot kernel: 4 CTAs / SM
+constexpr int F3_APRON = 16;                      // shared bytes each side of the tile (8 are generated, 4 are read)
 constexpr int F3_SROW = F3_TILE_WB + 2 * F3_APRON;
 constexpr int F3_ROWS = F3_TILE_H + 2;
-constexpr int F3_GROUPS_PER_ROW = F3_SROW / 8 + 1;  // +1: rows whose start is 4 (mod 8)
-
-__device__ __forceinline__ void unpack8(uint2 w, uint32_t (&v)[8]) {
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    v[i] = byte_of(w.x, i);
-    v[4 + i] = byte_of(w.y, i);
-  }
-}
-__device__ __forceinline__ uint2 pack8(const uint32_t (&v)[8]) {
-  return make_uint2(pack4(v[0], v[1], v[2], v[3]), pack4(v[4], v[5], v[6], v[7]));
-}
+constexpr int F3_GROUPS_PER_ROW = (F3_TILE_WB + 16) / 8 + 1;  // +1: rows whose start is 4 (mod 8)
+constexpr size_t F3_SMEM = (size_t)F3_ROWS * F3_SROW;
 
 // load the 8 bytes of group g of an image (4-byte aligned base, elems % 4 == 0)
 __device__ __forceinline__ uint2 load_group(const uint8_t* img, uint64_t elems, uint32_t g) {
@@ -51,10 +42,16 @@ __device__ __forceinline__ uint2 load_group(const uint8_t* img, uint64_t elems, 
   return w;
 }
 
-template <int KIND, int FILTER>
-__global__ void __launch_bounds__(F3_THREADS) k_fused3_any(ImageSet s, NoiseArgs na) {
-  using F = Filter3<FILTER>;
-  using Nz = NoiseOp<KIND, NM_GEN>;
+// Prologue: one 8-byte Philox group per thread and step, wherever it falls in the row (a row
+// that starts at 4 (mod 8) begins and ends in the middle of a group; the group is generated
+// whole and the half that belongs to the row is kept) - the PACKED operators of the hot kernel.
+// Filter: the band code of k_fused3 (b2d_fused3w.cu), 32-bit stores.
+template <int KIND, int FILTER, int KW>
+__global__ void __launch_bounds__(F3_THREADS, 4) k_fused3_any(ImageSet s, NoiseArgs na) {
+  using F = Filter3W<FILTER, KW>;
+  constexpr int TPB = F3_TILE_WB / (4 * KW);        // threads per band
+  constexpr int BANDS = F3_THREADS / TPB;
+  constexpr int BAND_H = F3_TILE_H / BANDS;
   extern __shared__ __align__(16) uint8_t smem[];
 
   const int tid = threadIdx.x;
@@ -63,27 +60,36 @@ __global__ void __launch_bounds__(F3_THREADS) k_fused3_any(ImageSet s, NoiseArgs
   const int img_local = image_of(s, blockIdx.z);
   const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
   const int cs = c0 - F3_APRON;                    // byte column held at smem row offset 0
-  const int col_lo = max(cs, 0), col_hi = min(c0 + F3_TILE_WB + F3_APRON, s.rowbytes);
+  const int col_lo = max(c0 - 8, 0), col_hi = min(c0 + F3_TILE_WB + 8, s.rowbytes);
   const int rows_needed = min(F3_ROWS, s.h - y0 + 2);
 
   // ---- prologue: noised bytes -> shared memory -----------------------------
+  // per tile row: first group and the byte column it starts at (64-bit arithmetic once per row)
+  __shared__ int2 s_row[F3_ROWS];
+  if (tid < rows_needed) {
+    const int ys = border_map(y0 - 1 + tid, s.h, F::BORDER);
+    const uint64_t fs = (uint64_t)ys * (uint64_t)s.rowbytes;     // flat index of the row start
+    const uint32_t g0 = (uint32_t)((fs + col_lo) >> 3);
+    s_row[tid] = make_int2((int)g0, (int)((int64_t)((uint64_t)g0 * 8u) - (int64_t)fs));
+  }
+  __syncthreads();
+  const uint32_t g_full = (uint32_t)(s.elems >> 3);              // groups that lie completely inside the image
+  const bool al8 = (reinterpret_cast<uintptr_t>(img) & 7u) == 0;
   for (int it = tid; it < rows_needed * F3_GROUPS_PER_ROW; it += F3_THREADS) {
     const int tr = it / F3_GROUPS_PER_ROW;
     const int gi = it - tr * F3_GROUPS_PER_ROW;
-    const int ys = border_map(y0 - 1 + tr, s.h, F::BORDER);
-    const uint64_t fs = (uint64_t)ys * (uint64_t)s.rowbytes;     // flat index of the row start
-    const uint32_t g = (uint32_t)((fs + col_lo) >> 3) + gi;
-    const int64_t cg = (int64_t)((uint64_t)g * 8u) - (int64_t)fs;  // byte column of the group start
+    const int2 ri = s_row[tr];
+    const uint32_t g = (uint32_t)ri.x + (uint32_t)gi;
+    const int cg = ri.y + 8 * gi;                                 // byte column of the group start
     if (cg >= col_hi) continue;
-    uint32_t v[8];
-    unpack8(load_group(img, s.elems, g), v);
+    uint2 raw;
+    if (al8 && g < g_full) raw = __ldg(reinterpret_cast<const uint2*>(img + (uint64_t)g * 8u));
+    else raw = load_group(img, s.elems, g);
     GroupCtx gc{(uint32_t)img_local, g, img};
-    Nz::apply8(na, gc, v);
-    const uint2 w = pack8(v);
-    uint8_t* srow = smem + tr * F3_SROW;
-    const int o0 = (int)cg - cs, o1 = o0 + 4;
-    if (cg >= col_lo && cg + 4 <= col_hi) *reinterpret_cast<uint32_t*>(srow + o0) = w.x;
-    if (cg + 4 >= col_lo && cg + 8 <= col_hi) *reinterpret_cast<uint32_t*>(srow + o1) = w.y;
+    const uint2 w = PackedNoise<KIND>::apply(na, gc, raw);
+    uint8_t* sdst = smem + tr * F3_SROW + (cg - cs);
+    if (cg >= col_lo) *reinterpret_cast<uint32_t*>(sdst) = w.x;             // (cg < col_hi: tested above)
+    if (cg + 4 >= col_lo && cg + 4 < col_hi) *reinterpret_cast<uint32_t*>(sdst + 4) = w.y;
   }
   __syncthreads();
 
@@ -91,45 +97,80 @@ __global__ void __launch_bounds__(F3_THREADS) k_fused3_any(ImageSet s, NoiseArgs
   const bool left_edge = (c0 == 0);
   const bool right_edge = (s.rowbytes <= c0 + F3_TILE_WB);
   if (left_edge || right_edge) {
-    for (int it = tid; it < rows_needed * 6; it += F3_THREADS) {
-      const int tr = it / 6, k = it - tr * 6, side = k / 3, ch = k - side * 3;
-      if ((side == 0 && !left_edge) || (side == 1 && !right_edge)) continue;
-      const int px = side == 0 ? -1 : s.w;
-      const int sp = border_map(px, s.w, F::BORDER);
-      uint8_t* srow = smem + tr * F3_SROW;
-      srow[px * 3 + ch - cs] = srow[sp * 3 + ch - cs];
+    if (tid < rows_needed) {                        // one thread per tile row, 3 bytes per side
+      uint8_t* srow = smem + tid * F3_SROW - cs;
+      if (left_edge) {
+        const int sp3 = 3 * border_map(-1, s.w, F::BORDER);
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) srow[ch - 3] = srow[sp3 + ch];
+      }
+      if (right_edge) {
+        const int sp3 = 3 * border_map(s.w, s.w, F::BORDER);
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) srow[s.rowbytes + ch] = srow[sp3 + ch];
+      }
     }
     __syncthreads();
   }
 
-  // ---- main loop: sliding 3-row window down the tile -----------------------
-  const int c = c0 + 4 * tid;
-  if (c >= s.rowbytes) return;
-  const uint8_t* sp = smem + F3_APRON + 4 * tid;
-  auto row_part = [&](int tr) {
-    const uint32_t wl = *reinterpret_cast<const uint32_t*>(sp + tr * F3_SROW - 4);
-    const uint32_t wc = *reinterpret_cast<const uint32_t*>(sp + tr * F3_SROW);
-    const uint32_t wr = *reinterpret_cast<const uint32_t*>(sp + tr * F3_SROW + 4);
-    return F::hpart(word_left3(wl, wc), wc, word_right3(wc, wr));
+  // ---- filter: a thread owns KW words of one band and slides down it -----------------
+  const int band = tid / TPB, q = tid - band * TPB;
+  const int c = c0 + 4 * KW * q;
+  const int o0 = band * BAND_H;                      // first output row (tile-relative) of the band
+  const int nrows = min(BAND_H, s.h - y0 - o0);
+  if (c >= s.rowbytes || nrows <= 0) return;
+  const uint8_t* sp = smem + F3_APRON + 4 * KW * q + o0 * F3_SROW;
+  auto load_row = [&](int tr, typename F::Part& p) {
+    const uint8_t* rp = sp + tr * F3_SROW;
+    uint32_t w[KW + 2];
+    w[0] = *reinterpret_cast<const uint32_t*>(rp - 4);
+    if (KW == 4) {
+      const uint4 v = *reinterpret_cast<const uint4*>(rp);
+      w[1] = v.x; w[2] = v.y; w[3] = v.z; w[KW] = v.w;
+    } else {
+      const uint2 v = *reinterpret_cast<const uint2*>(rp);
+      w[1] = v.x; w[KW] = v.y;
+    }
+    w[KW + 1] = *reinterpret_cast<const uint32_t*>(rp + 4 * KW);
+    RowLanes<KW> rl;
+    rl.split(w);
+    F::hpart(rl, p);
   };
-  typename F::Part p0 = row_part(0), p1 = row_part(1);
-  uint8_t* optr = s.out + (uint64_t)img_local * s.elems + (uint64_t)y0 * s.rowbytes + c;
-  const int nrows = min(F3_TILE_H, s.h - y0);
-#pragma unroll 4
-  for (int r = 0; r < nrows; ++r) {
-    const typename F::Part p2 = row_part(r + 2);
-    *reinterpret_cast<uint32_t*>(optr) = F::vcomb(p0, p1, p2);
+  typename F::Part p0, p1, p2;
+  load_row(0, p0);
+  load_row(1, p1);
+  uint8_t* optr = s.out + (uint64_t)img_local * s.elems + (uint64_t)(y0 + o0) * s.rowbytes + c;
+  const int nw = min(KW, (s.rowbytes - c) >> 2);     // valid words of the thread's column (rows are word multiples)
+#pragma unroll
+  for (int r = 0; r < BAND_H; ++r) {
+    if (r >= nrows) break;
+    typename F::Part& pt = (r % 3 == 0) ? p0 : (r % 3 == 1) ? p1 : p2;
+    typename F::Part& pm = (r % 3 == 0) ? p1 : (r % 3 == 1) ? p2 : p0;
+    typename F::Part& pb = (r % 3 == 0) ? p2 : (r % 3 == 1) ? p0 : p1;
+    load_row(r + 2, pb);
+    uint32_t o[KW];
+    F::vcomb(pt, pm, pb, o);
+#pragma unroll
+    for (int k = 0; k < KW; ++k)
+      if (k < nw) reinterpret_cast<uint32_t*>(optr)[k] = o[k];
     optr += s.rowbytes;
-    p0 = p1;
-    p1 = p2;
   }
 }
 
 template <int KIND, int FILTER>
 static cudaError_t launch_one(const ImageSet& s, const NoiseArgs& na, cudaStream_t st) {
+  constexpr int KW = FILTER == FK_MEDIAN3 ? 2 : 4;
+  static bool attr_done[64] = {};               // per device: the attribute lives in the context
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_done[dev & 63]) {
+    const cudaError_t e =
+        cudaFuncSetAttribute(k_fused3_any<KIND, FILTER, KW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F3_SMEM);
+    if (e != cudaSuccess) return e;
+    attr_done[dev & 63] = true;
+  }
   const dim3 grid((s.rowbytes + F3_TILE_WB - 1) / F3_TILE_WB, (s.h + F3_TILE_H - 1) / F3_TILE_H, s.count);
-  const size_t smem = (size_t)F3_ROWS * F3_SROW;
-  k_fused3_any<KIND, FILTER><<<grid, F3_THREADS, smem, st>>>(s, na);
+  k_fused3_any<KIND, FILTER, KW><<<grid, F3_THREADS, F3_SMEM, st>>>(s, na);
   count_launch();
   return cudaGetLastError();
 }
