@@ -45,8 +45,11 @@ __device__ __forceinline__ uint2 noise_group(const NoiseArgs& na, int img_local,
   return PackedNoise<KIND>::apply(na, gc, w);
 }
 
-template <int KIND, int FILTER, int KW>
+// A4: rows (and image bases) are only 4-byte aligned - rows of 4 (mod 8) bytes, W = 500.  Without a
+// generator (KIND == NK_NONE) groups do not matter, so the same tile code runs with 32-bit accesses.
+template <int KIND, int FILTER, int KW, bool A4 = false>
 __global__ void __launch_bounds__(FT_THREADS, 4) k_fused3(ImageSet s, NoiseArgs na) {
+  static_assert(!A4 || KIND == NK_NONE, "the 4-byte aligned variant has no generator");
   using F = Filter3W<FILTER, KW>;
   constexpr int TPB = FT_TWB / (4 * KW);            // threads per band
   constexpr int BANDS = FT_THREADS / TPB;
@@ -65,6 +68,32 @@ __global__ void __launch_bounds__(FT_THREADS, 4) k_fused3(ImageSet s, NoiseArgs 
     const int q = tid & 63, r0 = tid >> 6;
     const int c = c0 + 16 * q;
     const bool v0 = c < s.rowbytes, v1 = c + 8 < s.rowbytes;
+    if (A4) {
+      const int nwv = (s.rowbytes - c) >> 2;            // valid words of the thread's 16 bytes
+      if (v0) {
+#pragma unroll FT_UNROLL
+        for (int tr = r0; tr < rows; tr += 4) {
+          int ys = y0 - 1 + tr;
+          if (ys < 0 || ys >= s.h) ys = border_map(ys, s.h, F::BORDER);
+          const uint32_t* pw = reinterpret_cast<const uint32_t*>(img + (uint32_t)ys * (uint32_t)s.rowbytes + (uint32_t)c);
+          uint4 v = make_uint4(__ldg(pw), 0u, 0u, 0u);
+          if (nwv > 1) v.y = __ldg(pw + 1);
+          if (nwv > 2) v.z = __ldg(pw + 2);
+          if (nwv > 3) v.w = __ldg(pw + 3);
+          *reinterpret_cast<uint4*>(smem + tr * FT_SROW + FT_APRON + 16 * q) = v;
+        }
+      }
+      for (int it = tid; it < 2 * rows; it += FT_THREADS) {
+        const int tr = it >> 1, side = it & 1;
+        const int ca = side ? c0 + FT_TWB : c0 - 8;
+        if (ca < 0 || ca >= s.rowbytes) continue;
+        const int ys = border_map(y0 - 1 + tr, s.h, F::BORDER);
+        const uint32_t* pw = reinterpret_cast<const uint32_t*>(img + (uint32_t)ys * (uint32_t)s.rowbytes + (uint32_t)ca);
+        uint2 a = make_uint2(__ldg(pw), 0u);
+        if (ca + 4 < s.rowbytes) a.y = __ldg(pw + 1);
+        *reinterpret_cast<uint2*>(smem + tr * FT_SROW + (side ? FT_APRON + FT_TWB : FT_APRON - 8)) = a;
+      }
+    } else {
     if (v0) {
 #pragma unroll FT_UNROLL
       for (int tr = r0; tr < rows; tr += 4) {
@@ -90,6 +119,7 @@ __global__ void __launch_bounds__(FT_THREADS, 4) k_fused3(ImageSet s, NoiseArgs 
       const uint2 a = noise_group<KIND>(na, img_local, img, e >> 3, __ldg(reinterpret_cast<const uint2*>(img + e)));
       *reinterpret_cast<uint2*>(smem + tr * FT_SROW + (side ? FT_APRON + FT_TWB : FT_APRON - 8)) = a;
     }
+    }  // !A4
   }
   __syncthreads();
 
@@ -141,6 +171,7 @@ __global__ void __launch_bounds__(FT_THREADS, 4) k_fused3(ImageSet s, NoiseArgs 
   load_row(1, p1);
   uint8_t* optr = s.out + (uint64_t)img_local * s.elems + (uint64_t)(y0 + o0) * s.rowbytes + c;
   const bool full = c + 4 * KW <= s.rowbytes;        // rows are 8-byte multiples: else exactly 8 valid bytes
+  const int nw4 = min(KW, (s.rowbytes - c) >> 2);    // A4: valid words of the thread's column
 #pragma unroll
   for (int r = 0; r < BAND_H; ++r) {
     if (r >= nrows) break;
@@ -150,13 +181,19 @@ __global__ void __launch_bounds__(FT_THREADS, 4) k_fused3(ImageSet s, NoiseArgs 
     load_row(r + 2, pb);
     uint32_t o[KW];
     F::vcomb(pt, pm, pb, o);
-    *reinterpret_cast<uint2*>(optr) = make_uint2(o[0], o[1]);
-    if (KW == 4 && full) *reinterpret_cast<uint2*>(optr + 8) = make_uint2(o[KW - 2], o[KW - 1]);
+    if (A4) {
+#pragma unroll
+      for (int k = 0; k < KW; ++k)
+        if (k < nw4) reinterpret_cast<uint32_t*>(optr)[k] = o[k];
+    } else {
+      *reinterpret_cast<uint2*>(optr) = make_uint2(o[0], o[1]);
+      if (KW == 4 && full) *reinterpret_cast<uint2*>(optr + 8) = make_uint2(o[KW - 2], o[KW - 1]);
+    }
     optr += s.rowbytes;
   }
 }
 
-template <int KIND, int FILTER>
+template <int KIND, int FILTER, bool A4 = false>
 static cudaError_t launch_one(const ImageSet& s, const NoiseArgs& na, cudaStream_t st) {
   constexpr int KW = FILTER == FK_MEDIAN3 ? 2 : 4;
   static bool attr_done[64] = {};               // per device: the attribute lives in the context
@@ -164,12 +201,12 @@ static cudaError_t launch_one(const ImageSet& s, const NoiseArgs& na, cudaStream
   cudaGetDevice(&dev);
   if (!attr_done[dev & 63]) {
     const cudaError_t e =
-        cudaFuncSetAttribute(k_fused3<KIND, FILTER, KW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FT_SMEM);
+        cudaFuncSetAttribute(k_fused3<KIND, FILTER, KW, A4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FT_SMEM);
     if (e != cudaSuccess) return e;
     attr_done[dev & 63] = true;
   }
   const dim3 grid((s.rowbytes + FT_TWB - 1) / FT_TWB, (s.h + FT_TH - 1) / FT_TH, s.count);
-  k_fused3<KIND, FILTER, KW><<<grid, FT_THREADS, FT_SMEM, st>>>(s, na);
+  k_fused3<KIND, FILTER, KW, A4><<<grid, FT_THREADS, FT_SMEM, st>>>(s, na);
   count_launch();
   return cudaGetLastError();
 }
@@ -192,7 +229,21 @@ cudaError_t launch_fused3(int kind, int filter, const ImageSet& s, const NoiseAr
   if (s.count <= 0) return cudaSuccess;
   const bool fast = s.rowbytes % 8 == 0 && s.elems < (1ull << 31) &&
                     ((reinterpret_cast<uintptr_t>(s.in) | reinterpret_cast<uintptr_t>(s.out)) & 7u) == 0;
-  if (!fast) return launch_fused3_any(kind, filter, s, na, st);
+  if (!fast) {
+    // no generator, rows / bases only 4-byte aligned (W = 500): the tile kernel with 32-bit accesses
+    const bool fast4 = kind == NK_NONE && s.rowbytes % 4 == 0 && s.elems < (1ull << 31) &&
+                       ((reinterpret_cast<uintptr_t>(s.in) | reinterpret_cast<uintptr_t>(s.out)) & 3u) == 0;
+    static const char* a4_env = getenv("B2D_A4");      // B2D_A4=0: the group-wise kernel (cross-check)
+    if (fast4 && !(a4_env && a4_env[0] == '0')) {
+      switch (filter) {
+        case FK_GAUS3: return launch_one<NK_NONE, FK_GAUS3, true>(s, na, st);
+        case FK_MEAN3: return launch_one<NK_NONE, FK_MEAN3, true>(s, na, st);
+        case FK_MEDIAN3: return launch_one<NK_NONE, FK_MEDIAN3, true>(s, na, st);
+      }
+      return cudaErrorInvalidValue;
+    }
+    return launch_fused3_any(kind, filter, s, na, st);
+  }
   // Measured on B200 (scripts/bench_combos.py, 512 x 600 x 1000): without a generator the
   // row-marching persistent kernel (b2d_march3.cu) is 1.4-1.5x faster for gaus_blur / mean
   // (0.32 / 0.35 ms vs 0.48 / 0.50 ms: no apron rows, register prefetch); with a generator in the
