@@ -224,6 +224,8 @@ static cudaError_t launch_filter(int filter, const ImageSet& s, const NoiseArgs&
 cudaError_t launch_fused3_any(int kind, int filter, const ImageSet& s, const NoiseArgs& na, cudaStream_t st);
 cudaError_t launch_march3(int kind, int filter, const ImageSet& s, const NoiseArgs& na, cudaStream_t st);
 bool march3_supported(const ImageSet& s);
+bool march3_a4_supported(const ImageSet& s);
+cudaError_t launch_march3_a4(int filter, const ImageSet& s, const NoiseArgs& na, cudaStream_t st);
 
 cudaError_t launch_fused3(int kind, int filter, const ImageSet& s, const NoiseArgs& na, cudaStream_t st) {
   if (s.count <= 0) return cudaSuccess;
@@ -235,6 +237,9 @@ cudaError_t launch_fused3(int kind, int filter, const ImageSet& s, const NoiseAr
                        ((reinterpret_cast<uintptr_t>(s.in) | reinterpret_cast<uintptr_t>(s.out)) & 3u) == 0;
     static const char* a4_env = getenv("B2D_A4");      // B2D_A4=0: the group-wise kernel (cross-check)
     if (fast4 && !(a4_env && a4_env[0] == '0')) {
+      static const char* march4_env = getenv("B2D_MARCH");   // as below: gaus_blur / mean march, median tiles
+      if (filter != FK_MEDIAN3 && !(march4_env && march4_env[0] == '0') && march3_a4_supported(s))
+        return launch_march3_a4(filter, s, na, st);
       switch (filter) {
         case FK_GAUS3: return launch_one<NK_NONE, FK_GAUS3, true>(s, na, st);
         case FK_MEAN3: return launch_one<NK_NONE, FK_MEAN3, true>(s, na, st);

@@ -41,8 +41,11 @@ struct MarchGeom {
   int items;      // images * segs
 };
 
-template <int KIND, int FILTER>
+// A4: rows / image bases only 4-byte aligned (rows of 4 (mod 8) bytes, W = 500), no generator: the same
+// march with 32-bit global accesses; the last column then owns 4, 8, 12 or 16 valid bytes.
+template <int KIND, int FILTER, bool A4 = false>
 __global__ void __launch_bounds__(MARCH_MAX_THREADS, FILTER == FK_MEDIAN3 ? 2 : B2D_MARCH_MINB) k_march3(ImageSet s, NoiseArgs na, MarchGeom g) {
+  static_assert(!A4 || KIND == NK_NONE, "the 4-byte aligned variant has no generator");
   using F = Filter3W<FILTER, 4>;
   extern __shared__ __align__(16) uint8_t smem[];   // [2][MR][srow]
   const int tid = threadIdx.x;
@@ -50,6 +53,8 @@ __global__ void __launch_bounds__(MARCH_MAX_THREADS, FILTER == FK_MEDIAN3 ? 2 : 
   const int c = active ? 16 * tid : 0;               // idle threads shadow column 0 (loads only)
   const bool v1 = c + 8 < s.rowbytes;                // second 8-byte group of the unit is inside the row
   const bool first = tid == 0, last = tid == g.upr - 1;
+  const int nwv = min(4, (s.rowbytes - c) >> 2);     // A4: valid words of the unit (re-read the last one beyond)
+  const int o1 = nwv > 1 ? 1 : 0, o2 = nwv > 2 ? 2 : nwv - 1, o3 = nwv - 1;
   uint8_t* const my = smem + 16 + 16 * tid;          // this thread's unit in row 0 of buffer 0
   // border rows of the image (cv2 REFLECT_101: -1 -> 1, h -> h-2; REPLICATE: -1 -> 0, h -> h-1)
   const int top_src = F::BORDER == BORDER_REPLICATE ? 0 : 1;
@@ -78,8 +83,14 @@ __global__ void __launch_bounds__(MARCH_MAX_THREADS, FILTER == FK_MEDIAN3 ? 2 : 
 #pragma unroll
       for (int k = 0; k < MR; ++k) {
         const uint8_t* p = img + row_off(ch * MR + k);
-        ra[k] = __ldg(reinterpret_cast<const uint2*>(p));
-        rb[k] = __ldg(reinterpret_cast<const uint2*>(p + (v1 ? 8 : 0)));
+        if (A4) {
+          const uint32_t* pw = reinterpret_cast<const uint32_t*>(p);
+          ra[k] = make_uint2(__ldg(pw), __ldg(pw + o1));
+          rb[k] = make_uint2(__ldg(pw + o2), __ldg(pw + o3));
+        } else {
+          ra[k] = __ldg(reinterpret_cast<const uint2*>(p));
+          rb[k] = __ldg(reinterpret_cast<const uint2*>(p + (v1 ? 8 : 0)));
+        }
       }
     };
     fetch(0);
@@ -92,6 +103,10 @@ __global__ void __launch_bounds__(MARCH_MAX_THREADS, FILTER == FK_MEDIAN3 ? 2 : 
 #pragma unroll
         for (int k = 0; k < MR; ++k) {
           if (k >= jn) break;
+          if (A4) {
+            *reinterpret_cast<uint4*>(buf + k * g.srow) = make_uint4(ra[k].x, ra[k].y, rb[k].x, rb[k].y);
+            continue;
+          }
           const uint32_t e = row_off(ch * MR + k);
           GroupCtx g0{(uint32_t)img_local, e >> 3, img};
           const uint2 n0 = PackedNoise<KIND>::apply(na, g0, ra[k]);
@@ -123,7 +138,12 @@ __global__ void __launch_bounds__(MARCH_MAX_THREADS, FILTER == FK_MEDIAN3 ? 2 : 
           // pixel W for the last (which owns 16 or 8 valid bytes)
           if (first) w[0] = __byte_perm(q.x, q.y, kSelL);
           if (last) {
-            if (v1) w[5] = __byte_perm(q.z, q.w, kSelR);
+            if (A4) {                                // border pixel behind the nwv valid words
+              if (nwv == 4) w[5] = __byte_perm(w[3], w[4], kSelR);
+              else if (nwv == 3) w[4] = __byte_perm(w[2], w[3], kSelR);
+              else if (nwv == 2) w[3] = __byte_perm(w[1], w[2], kSelR);
+              else w[2] = __byte_perm(w[0], w[1], kSelR);
+            } else if (v1) w[5] = __byte_perm(q.z, q.w, kSelR);
             else w[3] = __byte_perm(q.x, q.y, kSelR);
           }
           RowLanes<4> rl;
@@ -132,8 +152,14 @@ __global__ void __launch_bounds__(MARCH_MAX_THREADS, FILTER == FK_MEDIAN3 ? 2 : 
           if (ch > 0 || k >= 2) {                    // rows j-2, j-1, j -> output row ya + j - 2
             uint32_t o[4];
             F::vcomb(pt, pm, pb, o);
-            *reinterpret_cast<uint2*>(optr) = make_uint2(o[0], o[1]);
-            if (v1) *reinterpret_cast<uint2*>(optr + 8) = make_uint2(o[2], o[3]);
+            if (A4) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i)
+                if (i < nwv) reinterpret_cast<uint32_t*>(optr)[i] = o[i];
+            } else {
+              *reinterpret_cast<uint2*>(optr) = make_uint2(o[0], o[1]);
+              if (v1) *reinterpret_cast<uint2*>(optr + 8) = make_uint2(o[2], o[3]);
+            }
             optr += s.rowbytes;
           }
         }
@@ -145,7 +171,7 @@ __global__ void __launch_bounds__(MARCH_MAX_THREADS, FILTER == FK_MEDIAN3 ? 2 : 
 
 struct MarchPlan { int grid, threads; size_t smem; MarchGeom g; };
 
-template <int KIND, int FILTER>
+template <int KIND, int FILTER, bool A4 = false>
 static cudaError_t launch_one(const ImageSet& s, const NoiseArgs& na, cudaStream_t st) {
   MarchPlan mp;
   mp.g.upr = (s.rowbytes + 15) / 16;
@@ -157,10 +183,10 @@ static cudaError_t launch_one(const ImageSet& s, const NoiseArgs& na, cudaStream
   cudaGetDevice(&dev);
   int& occ = occ_cache[dev & 63][mp.threads / 32];
   if (!occ) {
-    cudaError_t e = cudaFuncSetAttribute(k_march3<KIND, FILTER>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(k_march3<KIND, FILTER, A4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          2 * MR * (MARCH_MAX_THREADS * 16 + 32));
     if (e == cudaSuccess)
-      e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_march3<KIND, FILTER>, mp.threads, mp.smem);
+      e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_march3<KIND, FILTER, A4>, mp.threads, mp.smem);
     if (e != cudaSuccess) return e;
     if (occ < 1) occ = 1;
   }
@@ -183,7 +209,7 @@ static cudaError_t launch_one(const ImageSet& s, const NoiseArgs& na, cudaStream
   mp.g.seg_h = (s.h + best_segs - 1) / best_segs;
   mp.g.items = s.count * best_segs;
   mp.grid = std::min(mp.g.items, slots);
-  k_march3<KIND, FILTER><<<mp.grid, mp.threads, mp.smem, st>>>(s, na, mp.g);
+  k_march3<KIND, FILTER, A4><<<mp.grid, mp.threads, mp.smem, st>>>(s, na, mp.g);
   count_launch();
   return cudaGetLastError();
 }
@@ -202,6 +228,20 @@ bool march3_supported(const ImageSet& s) {
   return s.rowbytes % 8 == 0 && s.rowbytes >= 24 && s.rowbytes <= MARCH_MAX_THREADS * 16 && s.h >= 2 &&
          s.elems < (1ull << 31) &&
          ((reinterpret_cast<uintptr_t>(s.in) | reinterpret_cast<uintptr_t>(s.out)) & 7u) == 0;
+}
+
+// no generator, rows a multiple of 4 bytes only
+bool march3_a4_supported(const ImageSet& s) {
+  return s.rowbytes % 4 == 0 && s.rowbytes >= 24 && s.rowbytes <= MARCH_MAX_THREADS * 16 && s.h >= 2 &&
+         s.elems < (1ull << 31) &&
+         ((reinterpret_cast<uintptr_t>(s.in) | reinterpret_cast<uintptr_t>(s.out)) & 3u) == 0;
+}
+cudaError_t launch_march3_a4(int filter, const ImageSet& s, const NoiseArgs& na, cudaStream_t st) {
+  switch (filter) {
+    case FK_GAUS3: return launch_one<NK_NONE, FK_GAUS3, true>(s, na, st);
+    case FK_MEAN3: return launch_one<NK_NONE, FK_MEAN3, true>(s, na, st);
+  }
+  return cudaErrorInvalidValue;
 }
 
 cudaError_t launch_march3(int kind, int filter, const ImageSet& s, const NoiseArgs& na, cudaStream_t st) {

@@ -13,6 +13,8 @@ SHAPES = [(64, 96), (600, 1000), (375, 500), (33, 344), (32, 256), (31, 260), (1
           (37, 53), (70, 342), (129, 1027),
           # rows not word aligned (re-aligning tile kernel): row end 1-3 bytes either side of a tile boundary
           (500, 333), (500, 375), (35, 683), (34, 1025), (99, 341), (601, 999), (301, 3), (77, 5), (40, 1367),
+          # rows 4 (mod 8): 32-bit variants of the tile / march kernels; last column of 4 and 12 valid bytes
+          (9, 12), (50, 44), (40, 1364), (70, 1372),
           # fast tiled path (W % 8 == 0): multi-tile widths, row end on / next to a tile boundary, short bands
           (130, 2048), (65, 1368), (200, 8), (67, 1024), (3, 1032), (128, 344)]
 ORACLE = {"gaus_blur": D.gaus_blur_cv2, "mean": D.mean_cv2, "median": lambda u: D.median_cv2(u, 3)}
