@@ -68,6 +68,7 @@ __global__ void __launch_bounds__(FA_THREADS, 3) k_filter3_tile_any(ImageSet s) 
   // computed once per row, a lane then moves words lane, lane + 32, ... (one word per thread and
   // row, as in the first version, cost ~25 instructions of addressing per word).
   constexpr int NW = FA_TWB / 4 + FA_XW;            // words per tile row
+  const int nwl = min(NW, (s.rowbytes - c0 + 11) >> 2);   // words that hold bytes of the row (a narrow last tile loads little)
   const int warp = tid >> 5, lane = tid & 31;
 #pragma unroll 1
   for (int tr = warp; tr < rows; tr += FA_THREADS / 32) {
@@ -82,17 +83,17 @@ __global__ void __launch_bounds__(FA_THREADS, 3) k_filter3_tile_any(ImageSet s) 
 #pragma unroll
         for (int i = 0; i < (NW + 31) / 32; ++i) {
           const int j = lane + 32 * i;
-          if (j < NW) sdst[j] = __funnelshift_r(__ldg(wsrc + j), __ldg(wsrc + j + 1), sh);
+          if (j < nwl) sdst[j] = __funnelshift_r(__ldg(wsrc + j), __ldg(wsrc + j + 1), sh);
         }
       } else {
 #pragma unroll
         for (int i = 0; i < (NW + 31) / 32; ++i) {
           const int j = lane + 32 * i;
-          if (j < NW) sdst[j] = __ldg(wsrc + j);
+          if (j < nwl) sdst[j] = __ldg(wsrc + j);
         }
       }
     } else {                                        // first / last rows of an image: bytes outside it read as 0
-      for (int j = lane; j < NW; j += 32) {
+      for (int j = lane; j < nwl; j += 32) {
         const uint32_t a = guarded_word(base + 4 * j, img, img_end);
         const uint32_t b2 = phase ? guarded_word(base + 4 * j + 4, img, img_end) : 0u;
         sdst[j] = phase ? __funnelshift_r(a, b2, 8 * phase) : a;
