@@ -7,10 +7,11 @@
 // than the aligned tile kernel.  Here the rows are RE-ALIGNED on the way into shared memory, so the
 // filter phase is the packed-lane code of the hot kernel (b2d_filter3w.cuh) unchanged:
 //
-//   load   : every row of the tile starts at an arbitrary byte address; a warp takes a row, a lane
-//            reads the two aligned words that straddle its 4 bytes and funnel-shifts them by the
-//            row's phase (address & 3); 9 words per lane and row, 18 loads in flight.
-//   filter : as k_fused3 (bands, KW words per thread), results into a second shared tile.
+//   load   : every row of the tile starts at an arbitrary byte address; a warp takes a row and
+//            copies the ALIGNED words that cover it into shared memory with 4-byte cp.async (all
+//            rows of the tile in flight, no registers);
+//   filter : as k_fused3 (bands, KW words per thread), except that a row's words are funnel-shifted
+//            by the row's phase (address & 3) as they are read; results into a second shared tile.
 //   store  : the mirror image - words that lie completely inside the row are rebuilt with a
 //            funnel shift from the result tile and written as aligned 32-bit stores, the 0-3
 //            bytes at either end of the row segment as byte stores.
@@ -64,42 +65,32 @@ __global__ void __launch_bounds__(FA_THREADS, 3) k_filter3_tile_any(ImageSet s) 
     if (ys < 0 || ys >= s.h) ys = border_map(ys, s.h, F::BORDER);
     return img + (int64_t)ys * s.rowbytes + c0 - 8;                          // lands at shared offset APRON - 8
   };
-  // A WARP owns a tile row (rows warp, warp + 8, ...): address, phase and the in-image test are
-  // computed once per row, a lane then moves words lane, lane + 32, ... (one word per thread and
-  // row, as in the first version, cost ~25 instructions of addressing per word).
-  constexpr int NW = FA_TWB / 4 + FA_XW;            // words per tile row
-  const int nwl = min(NW, (s.rowbytes - c0 + 11) >> 2);   // words that hold bytes of the row (a narrow last tile loads little)
+  auto row_phase = [&](int tr) { return (unsigned)(reinterpret_cast<uintptr_t>(row_src(tr)) & 3u); };
+  // A WARP owns a tile row (rows warp, warp + 8, ...): the aligned words that cover it go to shared
+  // memory RAW with 4-byte cp.async - every row of the tile is in flight at once, nothing waits in
+  // registers (ncu r01i: the register version sat 15 of 25 cycles per instruction on the loads at
+  // 37 % occupancy).  The row's phase (address & 3) is applied by the readers below.
+  constexpr int NW = FA_TWB / 4 + FA_XW + 1;        // aligned words per tile row (one more than re-aligned words)
   const int warp = tid >> 5, lane = tid & 31;
+  const int nwl = min(NW, ((s.rowbytes - c0 + 11) >> 2) + 1);   // words that hold bytes of the row
 #pragma unroll 1
   for (int tr = warp; tr < rows; tr += FA_THREADS / 32) {
     const uint8_t* src = row_src(tr);
-    const unsigned phase = (unsigned)(reinterpret_cast<uintptr_t>(src) & 3u);
-    const uint8_t* base = src - phase;              // aligned; word j of the row is funnel(base[j], base[j + 1])
+    const uint8_t* base = src - (reinterpret_cast<uintptr_t>(src) & 3u);
     uint32_t* sdst = reinterpret_cast<uint32_t*>(smem + tr * FA_SROW + FA_APRON - 8);
-    const uint32_t* wsrc = reinterpret_cast<const uint32_t*>(base);
-    if (base >= img && base + 4 * (NW + 1) <= img_end) {
-      if (phase) {
-        const unsigned sh = 8u * phase;
+    if (base >= img && base + 4 * NW <= img_end) {
+      const uint32_t sa = (uint32_t)__cvta_generic_to_shared(sdst);
 #pragma unroll
-        for (int i = 0; i < (NW + 31) / 32; ++i) {
-          const int j = lane + 32 * i;
-          if (j < nwl) sdst[j] = __funnelshift_r(__ldg(wsrc + j), __ldg(wsrc + j + 1), sh);
-        }
-      } else {
-#pragma unroll
-        for (int i = 0; i < (NW + 31) / 32; ++i) {
-          const int j = lane + 32 * i;
-          if (j < nwl) sdst[j] = __ldg(wsrc + j);
-        }
+      for (int i = 0; i < (NW + 31) / 32; ++i) {
+        const int j = lane + 32 * i;
+        if (j < nwl)
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa + 4 * j), "l"(base + 4 * j) : "memory");
       }
     } else {                                        // first / last rows of an image: bytes outside it read as 0
-      for (int j = lane; j < nwl; j += 32) {
-        const uint32_t a = guarded_word(base + 4 * j, img, img_end);
-        const uint32_t b2 = phase ? guarded_word(base + 4 * j + 4, img, img_end) : 0u;
-        sdst[j] = phase ? __funnelshift_r(a, b2, 8 * phase) : a;
-      }
+      for (int j = lane; j < nwl; j += 32) sdst[j] = guarded_word(base + 4 * j, img, img_end);
     }
   }
+  asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
   __syncthreads();
 
   // ---- left / right image border: one apron pixel.  The row may end 1-3 bytes into the NEXT
@@ -109,7 +100,7 @@ __global__ void __launch_bounds__(FA_THREADS, 3) k_filter3_tile_any(ImageSet s) 
   const bool right_edge = (s.rowbytes <= c0 + FA_TWB + 3);
   if (left_edge || right_edge) {
     if (tid < rows) {
-      uint8_t* srow = smem + tid * FA_SROW + FA_APRON - c0;
+      uint8_t* srow = smem + tid * FA_SROW + FA_APRON - c0 + row_phase(tid);
       if (left_edge) {
         const int sp3 = 3 * border_map(-1, s.w, F::BORDER);
 #pragma unroll
@@ -134,16 +125,21 @@ __global__ void __launch_bounds__(FA_THREADS, 3) k_filter3_tile_any(ImageSet s) 
       const uint8_t* sp = smem + FA_APRON + 4 * KW * q + o0 * FA_SROW;
       auto load_row = [&](int tr, typename F::Part& p) {
         const uint8_t* rp = sp + tr * FA_SROW;
-        uint32_t w[KW + 2];
-        w[0] = *reinterpret_cast<const uint32_t*>(rp - 4);
+        const unsigned sh = 8u * row_phase(o0 + tr);
+        uint32_t R[KW + 3];                             // raw aligned words; tile byte t sits `phase` bytes further
+        R[0] = *reinterpret_cast<const uint32_t*>(rp - 4);
         if (KW == 4) {
           const uint4 v = *reinterpret_cast<const uint4*>(rp);
-          w[1] = v.x; w[2] = v.y; w[3] = v.z; w[KW] = v.w;
+          R[1] = v.x; R[2] = v.y; R[3] = v.z; R[4] = v.w;
         } else {
           const uint2 v = *reinterpret_cast<const uint2*>(rp);
-          w[1] = v.x; w[KW] = v.y;
+          R[1] = v.x; R[2] = v.y;
         }
-        w[KW + 1] = *reinterpret_cast<const uint32_t*>(rp + 4 * KW);
+        const uint2 t = *reinterpret_cast<const uint2*>(rp + 4 * KW);
+        R[KW + 1] = t.x; R[KW + 2] = t.y;
+        uint32_t w[KW + 2];
+#pragma unroll
+        for (int i = 0; i < KW + 2; ++i) w[i] = __funnelshift_r(R[i], R[i + 1], sh);   // (shift 0 returns R[i])
         RowLanes<KW> rl;
         rl.split(w);
         F::hpart(rl, p);
