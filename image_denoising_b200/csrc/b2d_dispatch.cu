@@ -167,6 +167,7 @@ int run_group(const RunCtx& c, const SpecGroup& g, int lo, int hi) {
     CK(launch_fused3(kind, f3, s, na, c.st));          // the one-pass hot path
     return B2D_OK;
   }
+  if (kind == NK_NONE) return denoise_u8(c, sp, s);    // `original_*`: nothing to stage, the denoiser reads the input
   // two-pass: noise -> stage (uint8) -> denoiser
   ImageSet ns = s;
   ns.out = stage;
