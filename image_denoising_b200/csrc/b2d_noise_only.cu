@@ -39,6 +39,61 @@ __device__ __forceinline__ void store_group_any(uint8_t* img, uint64_t elems, ui
   }
 }
 
+// generator mode keeps the group packed.  An image of odd size starts at any byte address: its groups
+// are read as the three aligned words around them (funnel shift by the phase) and written as one
+// aligned word plus 4 single bytes, instead of 8 + 8 byte accesses.
+__device__ __forceinline__ uint2 load_group_words(const uint8_t* img, uint64_t elems, uint32_t g) {
+  const uint64_t e = (uint64_t)g * 8u;
+  const uint8_t* p = img + e;
+  const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+  if (e + 8u <= elems) {
+    if ((a & 7u) == 0) return __ldg(reinterpret_cast<const uint2*>(p));
+    const unsigned ph = (unsigned)(a & 3u);
+    if (ph == 0) return make_uint2(__ldg(reinterpret_cast<const uint32_t*>(p)), __ldg(reinterpret_cast<const uint32_t*>(p + 4)));
+    if (e >= 4u && e + 12u <= elems) {            // the three words lie inside the image
+      const uint32_t* q = reinterpret_cast<const uint32_t*>(p - ph);
+      const uint32_t w0 = __ldg(q), w1 = __ldg(q + 1), w2 = __ldg(q + 2);
+      return make_uint2(__funnelshift_r(w0, w1, 8u * ph), __funnelshift_r(w1, w2, 8u * ph));
+    }
+  }
+  uint2 w = make_uint2(0u, 0u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    if (e + i < elems) w.x |= (uint32_t)__ldg(p + i) << (8 * i);
+    if (e + 4 + i < elems) w.y |= (uint32_t)__ldg(p + 4 + i) << (8 * i);
+  }
+  return w;
+}
+
+__device__ __forceinline__ void store_group_words(uint8_t* img, uint64_t elems, uint32_t g, uint2 w) {
+  const uint64_t e = (uint64_t)g * 8u;
+  uint8_t* p = img + e;
+  const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+  if (e + 8u <= elems) {
+    if ((a & 7u) == 0) { *reinterpret_cast<uint2*>(p) = w; return; }
+    const unsigned ph = (unsigned)(a & 3u);
+    if (ph == 0) {
+      *reinterpret_cast<uint32_t*>(p) = w.x;
+      *reinterpret_cast<uint32_t*>(p + 4) = w.y;
+      return;
+    }
+    const unsigned hb = 4u - ph;                  // head bytes in front of the aligned word
+#pragma unroll
+    for (unsigned i = 0; i < 3; ++i)
+      if (i < hb) p[i] = (uint8_t)(w.x >> (8u * i));
+    *reinterpret_cast<uint32_t*>(p + hb) = __funnelshift_r(w.x, w.y, 8u * hb);
+#pragma unroll
+    for (unsigned i = 0; i < 3; ++i)
+      if (i < ph) p[4u + hb + i] = (uint8_t)(w.y >> (8u * (hb + i)));
+    return;
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    if (e + i < elems) p[i] = (uint8_t)(w.x >> (8 * i));
+    if (e + 4 + i < elems) p[4 + i] = (uint8_t)(w.y >> (8 * i));
+  }
+}
+
 template <int KIND, int MODE>
 __global__ void __launch_bounds__(NO_THREADS) k_noise_only(ImageSet s, NoiseArgs na) {
   const int img_local = image_of(s, blockIdx.z);
@@ -46,21 +101,16 @@ __global__ void __launch_bounds__(NO_THREADS) k_noise_only(ImageSet s, NoiseArgs
   uint8_t* out = s.out ? s.out + (uint64_t)img_local * s.elems : nullptr;
   const uint32_t groups = (uint32_t)((s.elems + 7u) >> 3);
   for (uint32_t g = blockIdx.x * NO_THREADS + threadIdx.x; g < groups; g += gridDim.x * NO_THREADS) {
-    uint32_t v[8];
-    load_group_any(img, s.elems, g, v);
     GroupCtx gc{(uint32_t)img_local, g, img};
     if (MODE == NM_GEN) {
       // generator mode runs the packed operators, the same code the fused kernels run
-      const uint2 w = PackedNoise<KIND>::apply(
-          na, gc, make_uint2(pack4(v[0], v[1], v[2], v[3]), pack4(v[4], v[5], v[6], v[7])));
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        v[i] = byte_of(w.x, i);
-        v[4 + i] = byte_of(w.y, i);
-      }
-    } else {
-      NoiseOp<KIND, MODE>::apply8(na, gc, v);
+      const uint2 w = PackedNoise<KIND>::apply(na, gc, load_group_words(img, s.elems, g));
+      store_group_words(out, s.elems, g, w);
+      continue;
     }
+    uint32_t v[8];
+    load_group_any(img, s.elems, g, v);
+    NoiseOp<KIND, MODE>::apply8(na, gc, v);
     if (MODE != NM_DUMP) store_group_any(out, s.elems, g, v);
   }
 }

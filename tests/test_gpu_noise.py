@@ -135,3 +135,21 @@ def test_batch_split_and_seed_semantics(cuda):
     # one-pass fused kernel == noise pass followed by the denoiser
     two = api.apply(api.apply(batch, "gaussian_var1.0", seed=3), "original_median")
     assert torch.equal(full, two)
+
+
+@pytest.mark.parametrize("spec", ["gaussian_original_var1.0", "sap_original_var0.4", "speckle_original_var1.0",
+                                  "sap_mean_var0.4", "gaussian_median_var1.0"])
+def test_unaligned_image_base_same_bytes(cuda, spec):
+    """An image of odd size puts every second image of a batch at an odd address (funnel-shifted word
+    accesses); the same image alone, with the same global index, starts aligned.  Same bytes out."""
+    from image_denoising_b200 import api
+    h, w = 37, 53                                    # 5883 bytes per image
+    img = synth_batch(1, h, w, seed=77, kind="smooth")
+    batch = torch.from_numpy(np.concatenate([img] * 4)).to(cuda)
+    out4 = torch.empty_like(batch)
+    api.Plan(4, h, w, spec, 0).run(batch, out4, 11, 0)
+    one = torch.from_numpy(img).to(cuda)
+    for k in range(4):
+        out1 = torch.empty_like(one)
+        api.Plan(1, h, w, spec, 0).run(one, out1, 11, k)
+        assert torch.equal(out1[0], out4[k]), f"image {k} of the batch differs from the same image run alone"
