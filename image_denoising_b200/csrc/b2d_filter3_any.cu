@@ -65,7 +65,14 @@ __global__ void __launch_bounds__(FA_THREADS, 3) k_filter3_tile_any(ImageSet s) 
     if (ys < 0 || ys >= s.h) ys = border_map(ys, s.h, F::BORDER);
     return img + (int64_t)ys * s.rowbytes + c0 - 8;                          // lands at shared offset APRON - 8
   };
-  auto row_phase = [&](int tr) { return (unsigned)(reinterpret_cast<uintptr_t>(row_src(tr)) & 3u); };
+  // phase (address & 3) of tile row tr, in 32-bit arithmetic: (base + ys * rowbytes) mod 4
+  const unsigned ph_base = (unsigned)((reinterpret_cast<uintptr_t>(img) + (unsigned)c0 - 8u) & 3u);
+  const unsigned rb3 = (unsigned)s.rowbytes & 3u;
+  auto row_phase = [&](int tr) {
+    int ys = y0 - 1 + tr;
+    if (ys < 0 || ys >= s.h) ys = border_map(ys, s.h, F::BORDER);
+    return (ph_base + ((unsigned)ys & 3u) * rb3) & 3u;
+  };
   // A WARP owns a tile row (rows warp, warp + 8, ...): the aligned words that cover it go to shared
   // memory RAW with 4-byte cp.async - every row of the tile is in flight at once, nothing waits in
   // registers (ncu r01i: the register version sat 15 of 25 cycles per instruction on the loads at
