@@ -6,7 +6,7 @@ Layout: ``csrc/`` hand-written CUDA kernels + the C ABI (``include/b200denoise.h
 ``_lib`` ctypes binding, ``spec`` the grammar, ``api`` batch/host calls,
 ``minibatch`` / ``test_hook`` the reference-named shims.
 """
-from .spec import Spec, SpecError, parse, resolve_mix  # noqa: F401
+from .spec import Spec, SpecError, parse, resolve, resolve_mix  # noqa: F401
 
 
 def __getattr__(name):          # torch / CUDA are needed only by the compute entry points

@@ -20,6 +20,8 @@ NOISE = {"none": 0, "gaussian": 1, "poisson": 2, "sap": 3, "speckle": 4, "period
 DENOISE = {"none": 0, "gaus_blur": 1, "mean": 2, "median": 3, "bilateral": 4, "wavelet": 5}
 WAVELET = {"db1": 0, "haar": 0, "bior1.5": 1}
 COMPAT_SHADER_BGR = 1
+COMPAT_SAP_TRAIN06 = 2
+COMPAT_GAUSSIAN_RANDOM_LEVEL = 16     # host front-end flag (spec.resolve)
 LEVEL_SIZE = -1.0
 
 

@@ -15,7 +15,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from .spec import Spec, parse, resolve_mix
+from .spec import Spec, parse, resolve, resolve_mix  # noqa: F401
 
 DEFAULT_SEED = 3          # cfg.RNG_SEED, lib/model/config.py:255
 
@@ -143,13 +143,21 @@ def corrupt_host(images, spec, seed=DEFAULT_SEED, first_index=0, out=None, **ove
     return get_plan(n, h, w, spec, None, **overrides).run_host(images, out, seed, first_index)
 
 
-def corrupt(im, noise, seed=DEFAULT_SEED, index=0, side="test", rng=None, **overrides):
-    """Drop-in for one reference closure call: HxWx3 uint8 BGR ndarray in,
-    ndarray out (lib/model/test.py:1612-1784).  `mix` specs are resolved with
-    the reference's lists first."""
-    spec = resolve_mix(noise, side, rng)
+def corrupt(im, noise, seed=DEFAULT_SEED, index=0, side="test", rng=None, compat_flags=0, **overrides):
+    """Drop-in for one pass of the reference's per-image block: HxWx3 uint8 BGR ndarray in, ndarray
+    out (lib/model/test.py:1612-1831).  Concrete specs are one closure call.  `mix` specs are resolved
+    with the reference's lists, and a denoiser named next to `mix` runs the way the reference runs it:
+    as the post-denoise pass on the closure's uint8 result (``spec.resolve``).  ``compat_flags``:
+    ``spec.COMPAT_*`` (Q3 is resolved here, the others travel in the C spec)."""
+    concrete, post = resolve(noise, side, rng, compat_flags)
+    if compat_flags & ~16:
+        overrides = dict(overrides, compat_flags=compat_flags & ~16)
     im = np.ascontiguousarray(im)
-    return corrupt_host(im[None], spec, seed, index, **overrides)[0]
+    res = corrupt_host(im[None], concrete, seed, index, **overrides)
+    if post:
+        keep = {k: v for k, v in overrides.items() if k in ("ksize", "d", "sigma_color", "sigma_space", "wavelet", "levels")}
+        res = corrupt_host(res, "original_" + post, seed, index, **keep)
+    return res[0]
 
 
 def lab_convert(pixels, direction):

@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -17,6 +18,24 @@ static thread_local char g_err[512] = "";
 static thread_local uint64_t g_launches = 0;
 
 void count_launch() { ++g_launches; }
+
+int current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev;
+}
+
+int sm_count() {
+  static int sms[64] = {};
+  const int dev = current_device() & 63;
+  if (!sms[dev]) cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, current_device());
+  return sms[dev] > 0 ? sms[dev] : 148;
+}
+
+const char* knob(const char* name) {
+  static const bool enabled = [] { const char* e = getenv("B2D_DEBUG_KNOBS"); return e && e[0] == '1'; }();
+  return enabled ? getenv(name) : nullptr;
+}
 
 int fail(int code, const char* fmt, ...) {
   va_list ap;
@@ -174,7 +193,8 @@ extern "C" int b2d_stats(b2d_plan* plan, const uint8_t* d_ref, const uint8_t* d_
   if (!plan || !d_out || !d_checksum) return fail(B2D_ERR_INVALID, "b2d_stats: null argument");
   if (d_ref && !d_sse) return fail(B2D_ERR_INVALID, "b2d_stats: d_sse required with d_ref");
   if (plan->n == 0) return B2D_OK;
-  CK(cudaSetDevice(plan->device));
+  DeviceGuard guard(plan->device);
+  if (!guard.ok()) return fail_cuda(guard.err, "cudaSetDevice");
   cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
   CK(cudaMemsetAsync(d_checksum, 0, sizeof(uint64_t) * plan->n, st));
   if (d_sse) CK(cudaMemsetAsync(d_sse, 0, sizeof(double) * plan->n, st));

@@ -212,10 +212,12 @@ int run_bilateral(const b2d_spec& sp, const ImageSet& s, uint8_t* ws_tables, cud
   if (e != cudaSuccess) return fail_cuda(e, "bilateral tables");
   if (radius == BL_R) {
     const size_t smem = sizeof(uint32_t) * BL_PLANE + sizeof(float) * BL_CLASSES * BL_LUT;
-    static bool attr_set = false;
-    if (!attr_set) {
-      cudaFuncSetAttribute(k_bilateral_r4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      attr_set = true;
+    static bool attr_done[64] = {};             // per device: the attribute lives in the context
+    const int dev = current_device() & 63;
+    if (!attr_done[dev]) {
+      const cudaError_t ea = cudaFuncSetAttribute(k_bilateral_r4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (ea != cudaSuccess) return fail_cuda(ea, "bilateral shared-memory opt-in");
+      attr_done[dev] = true;
     }
     const dim3 grid((s.w + BL_TW - 1) / BL_TW, (s.h + BL_TH - 1) / BL_TH, s.count);
     k_bilateral_r4<<<grid, BL_THREADS, smem, st>>>(s, dtab + kLut2Off);

@@ -84,7 +84,9 @@ int run_group(const RunCtx& c, const SpecGroup& g, int lo, int hi) {
     case B2D_NOISE_SPECKLE: kind = NK_SPECKLE; na.p0 = (float)std::sqrt(sp.level); break;
     case B2D_NOISE_SAP:
       kind = NK_SAP; na.d0 = sp.level;
-      na.u0 = (uint32_t)std::max(0.0, std::min(32768.0, std::ceil(sp.level * 32768.0 - 0.5)));
+      if ((sp.compat_flags & B2D_COMPAT_SAP_TRAIN06) && sp.denoise == B2D_DENOISE_NONE && sp.level == 0.8)
+        na.d0 = 0.6;                                     // training closure, minibatch.py:367
+      na.u0 = (uint32_t)std::max(0.0, std::min(32768.0, std::ceil(na.d0 * 32768.0 - 0.5)));
       if (inject && !na.f1) return fail(B2D_ERR_INVALID, "sap with injected fields needs f0 (u1) and f1 (u2)");
       break;
     case B2D_NOISE_UNIFORM: kind = NK_UNIFORM; na.p0 = (float)sp.level; break;
@@ -98,7 +100,7 @@ int run_group(const RunCtx& c, const SpecGroup& g, int lo, int hi) {
     case B2D_NOISE_POISSON: {
       kind = NK_POISSON;
       float* par = reinterpret_cast<float*>(c.ws + p->off_par);
-      CK(launch_poisson_vals(s, reinterpret_cast<uint32_t*>(c.ws + p->off_bitmap), par, p->n, c.st));
+      CK(launch_poisson_vals(s, reinterpret_cast<uint32_t*>(c.ws + p->off_bitmap), par, c.st));
       na.img_par = par;
       if (inject) break;                               // injected counts: the per-element operator divides and clips
       // generator mode: alias-table sampler writes the corrupted uint8 image, the denoiser reads it
@@ -149,6 +151,11 @@ int run_group(const RunCtx& c, const SpecGroup& g, int lo, int hi) {
       if (sp.denoise == B2D_DENOISE_NONE) return B2D_OK;
       ImageSet ds = s;
       ds.in = stage;
+      if (sp.denoise == B2D_DENOISE_WAVELET) {           // quant_wavelet: denoise_wavelet(uint8 palette image), minibatch.py:501-537
+        NoiseArgs none{};
+        none.elems = p->elems;
+        return run_wavelet(*p, sp, ds, NK_NONE, NM_GEN, none, c.ws, c.st);
+      }
       return denoise_u8(c, sp, ds);
     }
     default: return fail(B2D_ERR_INVALID, "unknown noise %d", sp.noise);
@@ -197,7 +204,8 @@ extern "C" int b2d_run(b2d_plan* plan, const uint8_t* d_in, uint8_t* d_out, void
   if (plan->n == 0) return B2D_OK;
   if (!d_in || !d_out) return fail(B2D_ERR_INVALID, "b2d_run: null image buffer");
   if (!d_ws && plan->ws_bytes) return fail(B2D_ERR_INVALID, "b2d_run: workspace of %zu bytes required", plan->ws_bytes);
-  CK(cudaSetDevice(plan->device));
+  DeviceGuard guard(plan->device);
+  if (!guard.ok()) return fail_cuda(guard.err, "cudaSetDevice");
   RunCtx c{plan, d_in, d_out, static_cast<uint8_t*>(d_ws), fields, seed, first_global_image_index,
            static_cast<cudaStream_t>(cuda_stream)};
   return run_range(c, 0, plan->n);
@@ -211,36 +219,53 @@ extern "C" int b2d_run_host(b2d_plan* plan, const uint8_t* h_in, uint8_t* h_out,
   if (!plan) return fail(B2D_ERR_INVALID, "b2d_run_host: null plan");
   if (plan->n == 0) return B2D_OK;
   if (!h_in || !h_out) return fail(B2D_ERR_INVALID, "b2d_run_host: null image buffer");
-  CK(cudaSetDevice(plan->device));
+  DeviceGuard guard(plan->device);
+  if (!guard.ok()) return fail_cuda(guard.err, "cudaSetDevice");
   const size_t bytes = (size_t)plan->elems * plan->n;
   if (!plan->h_ready) {
     CK(cudaMalloc(&plan->h_d_in, bytes));
     CK(cudaMalloc(&plan->h_d_out, bytes));
     if (plan->ws_bytes) CK(cudaMalloc(&plan->h_d_ws, plan->ws_bytes));
-    for (int i = 0; i < 3; ++i) CK(cudaStreamCreateWithFlags(&plan->h_streams[i], cudaStreamNonBlocking));
+    for (int i = 0; i < 3; ++i) {
+      CK(cudaStreamCreateWithFlags(&plan->h_streams[i], cudaStreamNonBlocking));
+      CK(cudaEventCreateWithFlags(&plan->h_done[i], cudaEventDisableTiming));
+    }
     plan->h_ready = true;
   }
-  // chunks of >= 32 MiB (at least one image) so each copy runs at full PCIe rate (B2D_HOST_CHUNK_MB: tuning knob)
+  // chunks of >= 32 MiB (at least one image) so each copy runs at full PCIe rate (B2D_HOST_CHUNK_MB: diagnostic knob)
   static const uint64_t chunk_bytes = [] {
-    const char* e = getenv("B2D_HOST_CHUNK_MB");
+    const char* e = knob("B2D_HOST_CHUNK_MB");
     return (uint64_t)(e && atoi(e) > 0 ? atoi(e) : 32) << 20;
   }();
-  int per = (int)std::max<uint64_t>(1, chunk_bytes / plan->elems);
-  bool shared_ws = plan->need_aux;    // pre-pass / wavelet workspaces are shared by the whole batch: keep one chunk
-  for (const SpecGroup& g : plan->groups) shared_ws = shared_ws || g.spec.denoise == B2D_DENOISE_WAVELET;
-  if (shared_ws) per = plan->n;
+  const int per = (int)std::max<uint64_t>(1, chunk_bytes / plan->elems);
+  // Chunk k runs H2D -> kernels -> D2H on stream k % 3.  The KERNELS of consecutive chunks are chained with an
+  // event (chunk k + 1 computes after chunk k has computed): every piece of plan scratch that is not indexed by
+  // image - wavelet planes, bilateral / bloom / quant tables, the staging rows a pre-pass reuses - is therefore
+  // used by one chunk at a time, while the copies of the neighbouring chunks still overlap the kernels.  The
+  // kernels of one chunk fill the GPU, so nothing is lost by the chain.
+  int rc = B2D_OK;
+  cudaError_t ce = cudaSuccess;
   int k = 0;
-  for (int img0 = 0; img0 < plan->n; img0 += per, ++k) {
+  for (int img0 = 0; img0 < plan->n && rc == B2D_OK && ce == cudaSuccess; img0 += per, ++k) {
     const int cnt = std::min(per, plan->n - img0);
     cudaStream_t st = plan->h_streams[k % 3];
     const size_t off = (size_t)img0 * plan->elems, len = (size_t)cnt * plan->elems;
-    CK(cudaMemcpyAsync(plan->h_d_in + off, h_in + off, len, cudaMemcpyHostToDevice, st));
+    ce = cudaMemcpyAsync(plan->h_d_in + off, h_in + off, len, cudaMemcpyHostToDevice, st);
+    if (ce == cudaSuccess && k > 0) ce = cudaStreamWaitEvent(st, plan->h_done[(k - 1) % 3], 0);
+    if (ce != cudaSuccess) break;
     RunCtx c{plan, plan->h_d_in, plan->h_d_out, plan->h_d_ws, nullptr, seed, first_global_image_index, st};
-    const int rc = run_range(c, img0, cnt);
-    if (rc) return rc;
-    CK(cudaMemcpyAsync(h_out + off, plan->h_d_out + off, len, cudaMemcpyDeviceToHost, st));
+    rc = run_range(c, img0, cnt);
+    if (rc) break;
+    ce = cudaEventRecord(plan->h_done[k % 3], st);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(h_out + off, plan->h_d_out + off, len, cudaMemcpyDeviceToHost, st);
   }
-  for (int i = 0; i < 3; ++i) CK(cudaStreamSynchronize(plan->h_streams[i]));
+  // always drain all three streams: on an error the copies already queued still target the caller's memory
+  for (int i = 0; i < 3; ++i) {
+    const cudaError_t e = cudaStreamSynchronize(plan->h_streams[i]);
+    if (ce == cudaSuccess) ce = e;
+  }
+  if (rc) return rc;
+  if (ce != cudaSuccess) return fail_cuda(ce, "b2d_run_host");
   return B2D_OK;
 }
 
@@ -250,7 +275,8 @@ extern "C" int b2d_run_host(b2d_plan* plan, const uint8_t* h_in, uint8_t* h_out,
 extern "C" int b2d_noise_field(b2d_plan* plan, float* d_f0, float* d_f1, uint64_t seed,
                                uint64_t first_global_image_index, void* cuda_stream) {
   if (!plan || !d_f0) return fail(B2D_ERR_INVALID, "b2d_noise_field: null argument");
-  CK(cudaSetDevice(plan->device));
+  DeviceGuard guard(plan->device);
+  if (!guard.ok()) return fail_cuda(guard.err, "cudaSetDevice");
   cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
   for (const SpecGroup& g : plan->groups) {
     const b2d_spec& sp = g.spec;

@@ -226,7 +226,7 @@ static cudaError_t launch_tile_any(const ImageSet& s, cudaStream_t st) {
 cudaError_t launch_filter3_any(int filter, const ImageSet& s, cudaStream_t st) {
   if (s.count <= 0) return cudaSuccess;
   // B2D_FILTER_BYTES=1 forces the one-thread-per-byte kernel (the cross-check of the two in the tests)
-  static const char* bytes_env = getenv("B2D_FILTER_BYTES");
+  static const char* bytes_env = knob("B2D_FILTER_BYTES");
   if ((bytes_env && bytes_env[0] == '1') || s.elems >= (1ull << 31)) return launch_filter3_bytes(filter, s, st);
   switch (filter) {
     case FK_GAUS3: return launch_tile_any<FK_GAUS3>(s, st);

@@ -235,9 +235,9 @@ cudaError_t launch_fused3(int kind, int filter, const ImageSet& s, const NoiseAr
     // no generator, rows / bases only 4-byte aligned (W = 500): the tile kernel with 32-bit accesses
     const bool fast4 = kind == NK_NONE && s.rowbytes % 4 == 0 && s.elems < (1ull << 31) &&
                        ((reinterpret_cast<uintptr_t>(s.in) | reinterpret_cast<uintptr_t>(s.out)) & 3u) == 0;
-    static const char* a4_env = getenv("B2D_A4");      // B2D_A4=0: the group-wise kernel (cross-check)
+    static const char* a4_env = knob("B2D_A4");      // B2D_A4=0: the group-wise kernel (cross-check)
     if (fast4 && !(a4_env && a4_env[0] == '0')) {
-      static const char* march4_env = getenv("B2D_MARCH");   // as below: gaus_blur / mean march, median tiles
+      static const char* march4_env = knob("B2D_MARCH");   // as below: gaus_blur / mean march, median tiles
       if (filter != FK_MEDIAN3 && !(march4_env && march4_env[0] == '0') && march3_a4_supported(s))
         return launch_march3_a4(filter, s, na, st);
       switch (filter) {
@@ -254,7 +254,7 @@ cudaError_t launch_fused3(int kind, int filter, const ImageSet& s, const NoiseAr
   // (0.32 / 0.35 ms vs 0.48 / 0.50 ms: no apron rows, register prefetch); with a generator in the
   // prologue the tiles win (0.69 vs 0.78 ms for sap_mean: longer phases, fewer barriers), as they
   // do for the register-heavy median.  B2D_MARCH=0 / 1 forces one of the two (profiling).
-  static const char* march_env = getenv("B2D_MARCH");
+  static const char* march_env = knob("B2D_MARCH");
   const bool march = march_env ? march_env[0] == '1' : (kind == NK_NONE && filter != FK_MEDIAN3);
   if (march && march3_supported(s)) return launch_march3(kind, filter, s, na, st);
   switch (kind) {

@@ -339,7 +339,7 @@ __global__ void __launch_bounds__(256, 2) k_haar_apply(ImageSet s, NoiseArgs na,
 
 // ------------------------------------------------------------------ host side
 bool haar_supported(const b2d_plan& p, const b2d_spec& sp, int mode) {
-  static const bool off = [] { const char* e = getenv("B2D_HAAR"); return e && e[0] == '0'; }();
+  static const bool off = [] { const char* e = knob("B2D_HAAR"); return e && e[0] == '0'; }();
   if (off || mode != NM_GEN) return false;
   if (sp.wavelet != B2D_WAVELET_DB1 || sp.levels != 3) return false;
   if (p.h % 8 || p.w % 8 || p.h < 8 || p.w < 8) return false;
@@ -390,12 +390,7 @@ int run_haar(const b2d_plan& p, const ImageSet& s, int kind, const NoiseArgs& na
   HaarFinal fa;
   for (int i = 0; i < 3; ++i)
     for (int j = 0; j < 3; ++j) fa.inv[i][j] = inv[i][j];
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  }
+  const int sms = sm_count();
   for (int first = 0; first < s.count; first += chunk) {
     const int cnt = std::min(chunk, s.count - first);
     // two resident CTAs per SM: pick the CTA count per image that fills whole waves (cnt x per_image close to a

@@ -566,7 +566,8 @@ int b2d_jpeg_create(b2d_jpeg** out, int device, int max_n, int h, int w, int hos
     return fail(B2D_ERR_NO_DEVICE, "no CUDA device: the JPEG stage has no CPU fallback");
   }
   if (device < 0 || device >= ndev) return fail(B2D_ERR_INVALID, "device %d out of range (%d devices)", device, ndev);
-  CKJ(cudaSetDevice(device));
+  DeviceGuard guard(device);
+  if (!guard.ok()) return fail_cuda(guard.err, "cudaSetDevice");
   b2d_jpeg* D = new (std::nothrow) b2d_jpeg();
   if (!D) return fail(B2D_ERR_INVALID, "out of host memory");
   memset(D, 0, sizeof(*D));
@@ -593,7 +594,7 @@ int b2d_jpeg_create(b2d_jpeg** out, int device, int max_n, int h, int w, int hos
 
 void b2d_jpeg_destroy(b2d_jpeg* D) {
   if (!D) return;
-  cudaSetDevice(D->device);
+  DeviceGuard guard(D->device);
   if (D->pending) cudaEventSynchronize(D->uploaded);
   if (D->h_coef) cudaFreeHost(D->h_coef);
   if (D->h_desc) cudaFreeHost(D->h_desc);
@@ -622,7 +623,8 @@ int b2d_jpeg_decode(b2d_jpeg* D, int n, const uint8_t* const* data, const size_t
 
 static int jpeg_decode_impl(b2d_jpeg* D, int n, const uint8_t* const* data, const size_t* len, uint8_t* d_out, void* cuda_stream) {
   if (n == 0) return B2D_OK;
-  CKJ(cudaSetDevice(D->device));
+  DeviceGuard guard(D->device);
+  if (!guard.ok()) return fail_cuda(guard.err, "cudaSetDevice");
   if (D->pending) { CKJ(cudaEventSynchronize(D->uploaded)); D->pending = false; }   // the whole pinned ring is free again
   // Host threads decode images in order into a ring of `cap` staging slots (image i -> slot i % cap); the calling
   // thread uploads and launches chunk after chunk as soon as a chunk's images are done and releases a chunk's slots

@@ -21,6 +21,13 @@ __device__ __forceinline__ int image_of(const ImageSet& s, int z) { return s.lis
 
 // thread-local launch counter (bench.py's gpu_launches)
 void count_launch();
+// diagnostic environment knob (the list is in include/b200denoise.h): getenv(name) when
+// B2D_DEBUG_KNOBS=1 is set in the environment, nullptr otherwise - a production process cannot be
+// steered onto a cross-check kernel by a stray variable
+const char* knob(const char* name);
+// current device index (cudaGetDevice) and its SM count (cached per device)
+int current_device();
+int sm_count();
 
 // noise only (no denoiser), all modes
 cudaError_t launch_noise_only(int kind, int mode, const ImageSet& s, const NoiseArgs& na, cudaStream_t st);

@@ -407,7 +407,7 @@ static cudaError_t launch_median_t(const ImageSet& s, cudaStream_t st) {
 cudaError_t launch_median_k(const ImageSet& s, int k, cudaStream_t st) {
   if (s.count <= 0) return cudaSuccess;
   // B2D_MEDIAN_MODE = 1: one output at a time, 2: horizontal pairs, default: 2 x 2 blocks (measurement knob)
-  static const int mode = [] { const char* e = getenv("B2D_MEDIAN_MODE"); return e ? atoi(e) : 0; }();
+  static const int mode = [] { const char* e = knob("B2D_MEDIAN_MODE"); return e ? atoi(e) : 0; }();
   if (k == 5) return mode == 1 ? launch_median_t<5>(s, st) : mode == 2 ? launch_median_pairs<5>(s, st) : launch_median_blocks<5>(s, st);
   if (k == 7) return mode == 1 ? launch_median_t<7>(s, st) : mode == 2 ? launch_median_pairs<7>(s, st) : launch_median_blocks<7>(s, st);
   return cudaErrorInvalidValue;

@@ -155,7 +155,8 @@ int b2d_nms(int* keep_out, int* num_out, const float* boxes_host, int boxes_num,
     return fail(B2D_ERR_NO_DEVICE, "no CUDA device: NMS has no CPU fallback");
   }
   if (device_id < 0 || device_id >= ndev) return fail(B2D_ERR_INVALID, "device %d out of range (%d devices)", device_id, ndev);
-  CKN(cudaSetDevice(device_id));
+  DeviceGuard guard(device_id);
+  if (!guard.ok()) return fail_cuda(guard.err, "cudaSetDevice");
   cudaStream_t st = cudaStreamPerThread;
   const size_t cb = ((size_t)boxes_num + 63) / 64;
   const size_t box_bytes = (size_t)boxes_num * boxes_dim * sizeof(float), mask_bytes = (size_t)boxes_num * cb * sizeof(unsigned long long);

@@ -10,6 +10,22 @@ namespace b2d {
 int fail(int code, const char* fmt, ...);
 int fail_cuda(cudaError_t e, const char* what);
 
+// The ABI entry points run on the plan's device and leave the caller's current device as they found it
+// (under torch a changed current device silently redirects every later allocation).
+struct DeviceGuard {
+  int prev = -1;
+  cudaError_t err = cudaSuccess;
+  explicit DeviceGuard(int device) {
+    err = cudaGetDevice(&prev);
+    if (err == cudaSuccess && prev != device) err = cudaSetDevice(device);
+    else if (err == cudaSuccess) prev = -1;          // nothing to restore
+  }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+  bool ok() const { return err == cudaSuccess; }
+  DeviceGuard(const DeviceGuard&) = delete;
+  DeviceGuard& operator=(const DeviceGuard&) = delete;
+};
+
 struct SpecGroup {
   b2d_spec spec;
   std::vector<int> images;   // ascending batch indices
@@ -44,5 +60,6 @@ struct b2d_plan {
   // b2d_run_host resources (lazily created)
   uint8_t *h_d_in, *h_d_out, *h_d_ws;
   cudaStream_t h_streams[3];
+  cudaEvent_t h_done[3];     // "kernels of the chunk on stream i have finished" (chains the compute of consecutive chunks)
   bool h_ready;
 };

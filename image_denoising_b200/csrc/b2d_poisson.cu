@@ -156,16 +156,14 @@ __global__ void __launch_bounds__(PO_THREADS, 1) k_poisson(ImageSet s, NoiseArgs
 // `na.img_par` must already hold vals per image (launch_poisson_vals)
 cudaError_t launch_poisson(const ImageSet& s, const NoiseArgs& na, const uint8_t* tables, cudaStream_t st) {
   if (s.count <= 0) return cudaSuccess;
-  static bool attr_set = false;
-  static int sms = 0;
-  if (!attr_set) {
+  static bool attr_done[64] = {};               // per device: the attribute lives in the context
+  const int dev = current_device() & 63;
+  if (!attr_done[dev]) {
     cudaError_t e = cudaFuncSetAttribute(k_poisson, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PO_TABLE_BYTES);
     if (e != cudaSuccess) return e;
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    attr_set = true;
+    attr_done[dev] = true;
   }
+  const int sms = sm_count();
   const uint32_t ngroups = (uint32_t)((s.elems + 7) / 8);
   // one CTA per SM is resident (192 KB of shared memory): about two waves over the batch, and no
   // segment shorter than 16 passes of the CTA so the table load stays a small share

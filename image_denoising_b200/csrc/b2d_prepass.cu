@@ -53,24 +53,34 @@ __global__ void __launch_bounds__(256) k_unique_bitmap(ImageSet s, uint32_t* bit
   if (threadIdx.x < 8 && (bm[threadIdx.x] & ~seen)) atomicOr(gbm + threadIdx.x, bm[threadIdx.x]);
 }
 
-__global__ void k_poisson_vals(const uint32_t* bitmaps, float* vals, int n) {
+// the two small kernels touch only the images of this launch (b2d_run_host pipelines chunks of one batch
+// through one workspace: rows of other chunks may be in use by the previous chunk's kernels)
+__global__ void k_bitmap_clear(ImageSet s, uint32_t* bitmaps) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
+  if (i >= s.count * 8) return;
+  bitmaps[(size_t)image_of(s, i >> 3) * 8 + (i & 7)] = 0u;
+}
+
+__global__ void k_poisson_vals(ImageSet s, const uint32_t* bitmaps, float* vals) {
+  const int z = blockIdx.x * blockDim.x + threadIdx.x;
+  if (z >= s.count) return;
+  const int i = image_of(s, z);
   int cnt = 0;
-  for (int k = 0; k < 8; ++k) cnt += __popc(bitmaps[i * 8 + k]);
+  for (int k = 0; k < 8; ++k) cnt += __popc(bitmaps[(size_t)i * 8 + k]);
   int p = 1;
   while (p < cnt) p <<= 1;          // 2 ** ceil(log2(cnt))
   vals[i] = (float)p;
 }
 
-cudaError_t launch_poisson_vals(const ImageSet& s, uint32_t* bitmaps, float* vals, int n_batch, cudaStream_t st) {
-  cudaError_t e = cudaMemsetAsync(bitmaps, 0, sizeof(uint32_t) * 8 * n_batch, st);
-  if (e != cudaSuccess) return e;
+cudaError_t launch_poisson_vals(const ImageSet& s, uint32_t* bitmaps, float* vals, cudaStream_t st) {
+  if (s.count <= 0) return cudaSuccess;
+  k_bitmap_clear<<<(s.count * 8 + 255) / 256, 256, 0, st>>>(s, bitmaps);
+  count_launch();
   uint32_t bx = (uint32_t)((s.elems + 256 * 16 * 8 - 1) / (256 * 16 * 8));   // 8 x 16-byte loads per thread
   if (bx < 1) bx = 1;
   k_unique_bitmap<<<dim3(bx, 1, s.count), 256, 0, st>>>(s, bitmaps);
   count_launch();
-  k_poisson_vals<<<(n_batch + 127) / 128, 128, 0, st>>>(bitmaps, vals, n_batch);
+  k_poisson_vals<<<(s.count + 127) / 128, 128, 0, st>>>(s, bitmaps, vals);
   count_launch();
   return cudaGetLastError();
 }

@@ -20,7 +20,7 @@ void alias_row_256(const double* P, uint16_t* row);
 int gamma_folds(double scale);
 cudaError_t upload_gamma_table(double scale, uint8_t** d_table);
 cudaError_t launch_poisson(const ImageSet& s, const NoiseArgs& na, const uint8_t* tables, cudaStream_t st);
-cudaError_t launch_poisson_vals(const ImageSet& s, uint32_t* bitmaps, float* vals, int n_batch, cudaStream_t st);
+cudaError_t launch_poisson_vals(const ImageSet& s, uint32_t* bitmaps, float* vals, cudaStream_t st);
 cudaError_t launch_periodic_table(uint8_t* tab, uint64_t n, double lim, cudaStream_t st);
 cudaError_t launch_brownian_field(const ImageSet& s, const NoiseArgs& na, const BrownianArgs& ba, bool inject,
                                   cudaStream_t st);

@@ -35,6 +35,18 @@ static int validate_spec(const b2d_spec& s, int h, int w) {
     return fail(B2D_ERR_INVALID, "gamma scale %g outside (0, 100]", s.level);
   if ((s.noise == B2D_NOISE_GAUSSIAN || s.noise == B2D_NOISE_SPECKLE) && !(s.level >= 0.0 && s.level <= 100.0))
     return fail(B2D_ERR_INVALID, "gaussian / speckle var must be in [0, 100] (packed generator range)");
+  if (s.denoise == B2D_DENOISE_WAVELET) {
+    if (s.wavelet != B2D_WAVELET_DB1 && s.wavelet != B2D_WAVELET_BIOR15)
+      return fail(B2D_ERR_INVALID, "spec.wavelet %d: 0 (db1) or 1 (bior1.5)", s.wavelet);
+    if (s.levels < 0 || s.levels > 8) return fail(B2D_ERR_INVALID, "spec.levels %d outside [0, 8] (0 = skimage's rule)", s.levels);
+  }
+  if (s.noise == B2D_NOISE_PERIODIC && s.level != B2D_LEVEL_SIZE && !(s.level > 0.0))
+    return fail(B2D_ERR_INVALID, "periodic limit must be > 0 or B2D_LEVEL_SIZE");
+  if (s.noise == B2D_NOISE_BROWNIAN && !(s.level > 0.0)) return fail(B2D_ERR_INVALID, "brownian dt must be > 0");
+  if (s.noise == B2D_NOISE_SAP && !(s.level >= 0.0 && s.level <= 1.0))
+    return fail(B2D_ERR_INVALID, "s&p amount must be in [0, 1]");
+  if ((s.noise == B2D_NOISE_UNIFORM || s.noise == B2D_NOISE_RAYLEIGH) && !(s.level >= 0.0 && s.level <= 16.0))
+    return fail(B2D_ERR_INVALID, "uniform / rayleigh level must be in [0, 16] (packed generator range)");
   (void)w;
   return B2D_OK;
 }
@@ -50,7 +62,8 @@ extern "C" int b2d_plan_create(b2d_plan** out, int device, int n, int h, int w, 
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
     return fail(B2D_ERR_NO_DEVICE, "no CUDA device: libb200denoise has no CPU fallback");
   if (device < 0 || device >= ndev) return fail(B2D_ERR_INVALID, "device %d out of range (%d devices)", device, ndev);
-  CK(cudaSetDevice(device));
+  DeviceGuard guard(device);
+  if (!guard.ok()) return fail_cuda(guard.err, "cudaSetDevice");
   for (int i = 0; i < n_specs; ++i) {
     const int rc = validate_spec(specs[i], h, w);
     if (rc) return rc;
@@ -157,7 +170,7 @@ extern "C" int b2d_plan_workspace_bytes(const b2d_plan* plan, size_t* bytes) {
 
 extern "C" void b2d_plan_destroy(b2d_plan* p) {
   if (!p) return;
-  cudaSetDevice(p->device);
+  DeviceGuard guard(p->device);
   for (SpecGroup& g : p->groups)
     if (g.d_list) cudaFree(g.d_list);
   for (PeriodicTable& t : p->periodic)
@@ -169,7 +182,10 @@ extern "C" void b2d_plan_destroy(b2d_plan* p) {
   if (p->h_d_out) cudaFree(p->h_d_out);
   if (p->h_d_ws) cudaFree(p->h_d_ws);
   if (p->h_ready)
-    for (int i = 0; i < 3; ++i) cudaStreamDestroy(p->h_streams[i]);
+    for (int i = 0; i < 3; ++i) {
+      cudaStreamDestroy(p->h_streams[i]);
+      cudaEventDestroy(p->h_done[i]);
+    }
   delete p;
 }
 

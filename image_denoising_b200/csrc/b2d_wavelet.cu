@@ -937,8 +937,8 @@ int run_wavelet(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, int ki
       default: return fail(B2D_ERR_INVALID, "wavelet: bad noise operator %d", kind);
     }
     count_launch();
-    static const bool generic = [] { const char* e = getenv("B2D_WV_GENERIC"); return e && e[0] == '1'; }();
-    static const bool fused = [] { const char* e = getenv("B2D_WV_FUSED"); return !(e && e[0] == '0'); }();
+    static const bool generic = [] { const char* e = knob("B2D_WV_GENERIC"); return e && e[0] == '1'; }();
+    static const bool fused = [] { const char* e = knob("B2D_WV_FUSED"); return !(e && e[0] == '0'); }();
     const bool db1 = sp.wavelet == B2D_WAVELET_DB1;
     auto cdiv = [](int a, int b) { return (unsigned)((a + b - 1) / b); };
     for (int l = 1; l <= g.L; ++l) {

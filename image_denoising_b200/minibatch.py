@@ -20,7 +20,7 @@ import numpy.random as npr
 from . import api
 from .blob import im_list_to_blob, prep_im_for_blob
 from .config import cfg
-from .spec import POST_DENOISE_ORDER, resolve_mix
+from .spec import POST_DENOISE_ORDER, resolve
 
 
 def _load(entry):
@@ -72,7 +72,9 @@ def _to_device_batch(items, dev):
 def corrupt_images(imgs, specs, indices, side="train", double_filter=False, rng=None):
     """imgs: list of HxWx3 uint8 BGR arrays -> list of corrupted + denoised uint8 arrays.
     Images of equal shape go to the GPU as one batch (per-image specs)."""
-    specs = [resolve_mix(s, side, rng) for s in specs]
+    resolved = [resolve(s, side, rng) for s in specs]
+    specs = [r[0] for r in resolved]
+    posts = [r[1] for r in resolved]                     # mix + denoiser: the reference's post-denoise pass
     out = [None] * len(imgs)
     by_shape = {}
     for i, im in enumerate(imgs):
@@ -86,11 +88,12 @@ def corrupt_images(imgs, specs, indices, side="train", double_filter=False, rng=
         else:
             for j, i in enumerate(idx):
                 res[j] = api.corrupt_host(batch[j:j + 1], specs[i], seed=cfg.RNG_SEED, first_index=indices[i])[0]
-        if double_filter:
-            for j, i in enumerate(idx):
+        for j, i in enumerate(idx):
+            post = posts[i]
+            if post is None and double_filter and isinstance(specs[i], str):
                 post = next((d for d in POST_DENOISE_ORDER if d in specs[i]), None)
-                if post:
-                    res[j] = api.corrupt_host(res[j:j + 1], "original_" + post)[0]
+            if post:
+                res[j] = api.corrupt_host(res[j:j + 1], "original_" + post)[0]
         for j, i in enumerate(idx):
             out[i] = res[j]
     return out
@@ -123,7 +126,9 @@ def _get_image_blob_device(roidb, scale_inds, double_filter=False, device_decode
     import torch
     from .blob import blob_shape, prep_blob_device
     imgs = [_load_for_device(r) if device_decode else _load(r) for r in roidb]
-    specs = [resolve_mix(r.get('noise_type', 'original'), "train", None) for r in roidb]
+    resolved = [resolve(r.get('noise_type', 'original'), "train", None) for r in roidb]
+    specs = [r[0] for r in resolved]
+    posts = [r[1] for r in resolved]
     indices = [int(r.get('index', i)) for i, r in enumerate(roidb)]
     targets = [cfg.TRAIN.SCALES[scale_inds[i]] for i in range(len(roidb))]
     shapes = [blob_shape(im.shape[0], im.shape[1], targets[i], cfg.TRAIN.MAX_SIZE) for i, im in enumerate(imgs)]
@@ -141,11 +146,12 @@ def _get_image_blob_device(roidb, scale_inds, double_filter=False, device_decode
         else:
             res = torch.cat([api.apply(batch[j:j + 1], specs[i], seed=cfg.RNG_SEED, first_index=indices[i])
                              for j, i in enumerate(idx)])
-        if double_filter:
-            for j, i in enumerate(idx):
+        for j, i in enumerate(idx):
+            post = posts[i]
+            if post is None and double_filter and isinstance(specs[i], str):
                 post = next((d for d in POST_DENOISE_ORDER if d in specs[i]), None)
-                if post:
-                    res[j:j + 1] = api.apply(res[j:j + 1].contiguous(), "original_" + post)
+            if post:
+                res[j:j + 1] = api.apply(res[j:j + 1].contiguous(), "original_" + post)
         flips = [bool(roidb[i].get('flipped', False)) for i in idx]
         whole = idx == list(range(idx[0], idx[0] + len(idx)))
         if whole:                                              # the group is a contiguous slab of the blob

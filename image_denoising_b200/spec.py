@@ -116,11 +116,18 @@ def parse(spec, **overrides):
     return Spec(noise, den, level, **overrides)
 
 
+COMPAT_SHADER_BGR = _lib.COMPAT_SHADER_BGR
+COMPAT_SAP_TRAIN06 = _lib.COMPAT_SAP_TRAIN06
+COMPAT_GAUSSIAN_RANDOM_LEVEL = _lib.COMPAT_GAUSSIAN_RANDOM_LEVEL     # Q3, host front-end flag
+_Q3_LIST = ['gaussian_var0.1', 'gaussian_var1.0', 'gaussian_var1.5']   # minibatch.py:1575-1576, test.py:1678-1679
+
+
 def resolve_mix(spec, side="test", rng=None):
     """The `mix` branch: pick a noise-only spec (test.py:1612-1639,
     minibatch.py:1518-1547).  ``rng``: a ``random.Random`` (the reference uses
-    the never-seeded global ``random``).  Non-mix specs pass through; the
-    reference's `gaussian` quirk Q3 (level ignored) is NOT reproduced."""
+    the never-seeded global ``random``).  Non-mix specs pass through.  A
+    denoiser named in a mix spec is NOT part of the returned string: the
+    reference applies it in its post-denoise pass - use ``resolve`` to get it."""
     if "mix" not in spec:
         return spec
     rng = rng or _random
@@ -128,3 +135,40 @@ def resolve_mix(spec, side="test", rng=None):
         if key in spec:
             return rng.choice(MIX_LISTS[side][key])
     raise SpecError("mix spec %r names none of var_low/var_medium/var_high/var_all" % spec)
+
+
+def post_denoiser(spec, side="train"):
+    """The denoiser the reference's post-denoise pass applies to the closure's result for the
+    top-level ``spec`` string (first match of the elif chain), or None.  Training side: all five are
+    live (minibatch.py:1636-1663).  Test side: the gaus_blur / mean / median / bilateral branches
+    only print (their cv2 calls are commented out, test.py:1787-1819); `wavelet` is live
+    (test.py:1805-1812) and is reached only when none of gaus_blur / mean / median is in the spec."""
+    if isinstance(spec, Spec):
+        return None
+    d = next((d for d in POST_DENOISE_ORDER if d in spec), None)
+    if side == "test" and d != "wavelet":
+        return None
+    return d
+
+
+def resolve(spec, side="test", rng=None, compat_flags=0):
+    """-> (concrete spec, post) for one top-level ``--noise`` string.
+
+    * `mix` specs: ``concrete`` = the noise-only string drawn from the reference's list, ``post`` = the
+      denoiser its post-denoise pass runs on that closure's uint8 result (``noise_mix_var_low_mean``
+      -> e.g. ``('sap_var0.2', 'mean')``).  This is the only way the reference denoises a mix.
+    * ``compat_flags & COMPAT_GAUSSIAN_RANDOM_LEVEL`` (quirk Q3, minibatch.py:1575-1580,
+      test.py:1678-1682): any spec containing `gaussian` ignores its own level and denoiser, draws one
+      of the three noise-only gaussian specs with ``random.choice`` and leaves the denoiser to the
+      post pass.  Off by default.
+    * everything else: ``(spec, None)`` - one closure call, at most one denoise pass (the canonical
+      semantics); the training-side second filtering (Q1) stays opt-in
+      (``double_filter=True`` in minibatch.py)."""
+    if isinstance(spec, Spec):
+        return spec, None
+    rng = rng or _random
+    if "mix" in spec:
+        return resolve_mix(spec, side, rng), post_denoiser(spec, side)
+    if (compat_flags & COMPAT_GAUSSIAN_RANDOM_LEVEL) and "gaussian" in spec:
+        return rng.choice(_Q3_LIST), post_denoiser(spec, side)
+    return spec, None

@@ -67,10 +67,14 @@ def corrupt_paths_for_test_device(paths, noise, first_index=0, **overrides):
     `cv2.imread` (test.py:191) = `b2d_jpeg_decode` (bit-exact), closures (test.py:193-1831) = `b2d_run`.
     Returns the (N, H, W, 3) uint8 CUDA tensor `im_detect` would get image by image (feed `get_test_blob_device`)."""
     from . import jpeg
-    from .spec import resolve_mix
+    from .spec import resolve
     batch = jpeg.imread_batch(paths)
-    specs = [resolve_mix(noise, "test", None) for _ in paths]
-    return api.apply(batch, specs, seed=cfg.RNG_SEED, first_index=first_index, **overrides)
+    resolved = [resolve(noise, "test", None) for _ in paths]
+    res = api.apply(batch, [r[0] for r in resolved], seed=cfg.RNG_SEED, first_index=first_index, **overrides)
+    post = resolved[0][1] if resolved else None            # same top-level string: same post pass for every image
+    if post:                                               # `noise_mix_*_wavelet`: the live post pass of test.py:1805-1812
+        res = api.apply(res, "original_" + post, seed=cfg.RNG_SEED, first_index=first_index)
+    return res
 
 
 def nms_for_test(cls_dets, thresh=None):

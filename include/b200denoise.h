@@ -73,11 +73,29 @@ typedef enum {
 
 enum { B2D_WAVELET_DB1 = 0, B2D_WAVELET_BIOR15 = 1 };
 
-/* compat_flags */
+/* compat_flags: reference quirks that are NOT part of the canonical semantics, opt-in */
 enum {
-  B2D_COMPAT_SHADER_BGR = 1, /* keep BGR order for `shader` (reference returns RGB, quirk Q5) */
-  B2D_COMPAT_SAP_SVP06 = 2   /* salt_vs_pepper 0.6 (training noise-only sap 0.8, minibatch.py:367) */
+  B2D_COMPAT_SHADER_BGR = 1,  /* keep BGR order for `shader` (the reference returns RGB, quirk Q5)              */
+  B2D_COMPAT_SAP_TRAIN06 = 2, /* noise-only `sap_var0.8` draws with amount 0.6, as the TRAINING closure does
+                                 (lib/roi_data_layer/minibatch.py:367; test.py:434 uses 0.8)                    */
+  B2D_COMPAT_GAUSSIAN_RANDOM_LEVEL = 16 /* quirk Q3 (minibatch.py:1575-1580, test.py:1678-1682): a spec that
+                                 contains `gaussian` ignores its own level and denoiser and draws one of
+                                 gaussian_var{0.1,1.0,1.5} with Python's random.choice.  HOST front-end flag
+                                 (image_denoising_b200.spec.resolve): the choice uses the caller's `random`
+                                 state, which does not exist below this ABI; b2d_plan_create ignores the bit. */
 };
+
+/* Diagnostic environment variables.  They select cross-check kernels inside b2d_run / b2d_run_host and
+ * are honoured ONLY when B2D_DEBUG_KNOBS=1 is also set (read once per process); otherwise ignored.
+ *   B2D_MARCH=0|1        3x3 filters: force the tile kernel (0) or the row-marching kernel (1)
+ *   B2D_A4=0             rows of 4 (mod 8) bytes: group-wise kernel instead of the 32-bit tile / marching kernels
+ *   B2D_FILTER_BYTES=1   W % 4 != 0: one-thread-per-byte 3x3 filter instead of the re-aligning tile kernel
+ *   B2D_MEDIAN_MODE=1|2  median 5 / 7: one-output (1) or pair (2) kernels instead of the 2x2-block kernel
+ *   B2D_HAAR=0           db1 / 3 levels: general multi-pass wavelet path instead of the register-resident one
+ *   B2D_WV_FUSED=0       general wavelet path: one launch per axis instead of the fused 2-D level kernels
+ *   B2D_WV_GENERIC=1     general wavelet path: per-output reference kernels
+ *   B2D_HOST_CHUNK_MB=n  b2d_run_host: pipeline chunk size in MiB (default 32)
+ * The Python loader additionally reads B2D_LIB (path of an alternative build of this library; not gated). */
 
 /* B2D_LEVEL_SIZE: periodic `varsize` (L = H*W*3, minibatch.py:1066) */
 #define B2D_LEVEL_SIZE (-1.0)

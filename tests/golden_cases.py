@@ -37,26 +37,24 @@ def inputs():
 
 
 def deterministic_specs():
-    specs = ["original_gaus_blur", "original_mean", "original_median", "original_bilateral", "original_wavelet", "shader"]
-    for lvl in ("3.14", "100", "size"):
-        specs += ["periodic_var" + lvl, "periodic_mean_var" + lvl]
-    specs += ["periodic_median_var100", "periodic_gaus_blur_var100"]
-    return specs
+    """retain_original (+ each post-denoise pass, minibatch.py:1636-1662) and shader; the periodic ladder is
+    deterministic too but lives with the other noises in stochastic_specs()."""
+    return ["original", "original_gaus_blur", "original_mean", "original_median", "original_bilateral", "original_wavelet",
+            "shader"]
 
 
 def stochastic_specs():
+    """The WHOLE ladder of the reference: every noise closure x {noise only, wavelet, gaus_blur, mean, median,
+    bilateral} x each of its three `'var<L>' in spec` levels (lib/roi_data_layer/minibatch.py:87-1484, twins in
+    lib/model/test.py:193-1588) - 9 x 6 x 3 + poisson x 6 = 168 specs, no cell skipped."""
+    from oracle import closures as C
     specs = []
-    for noise, lvl in LEVEL_MID.items():
-        for den in ("", "_gaus_blur", "_mean", "_median", "_bilateral", "_wavelet"):
-            if noise == "brownian" and den in ("_bilateral", "_wavelet"):
-                continue
-            specs.append("%s%s_var%s" % (noise, den, lvl))
-    # the other two levels of every `'var<L>' in spec` ladder (minibatch.py:98-199 and twins), noise only and + median
-    for noise, levels in OTHER_LEVELS.items():
-        for lvl in levels:
-            specs += ["%s_var%s" % (noise, lvl), "%s_median_var%s" % (noise, lvl)]
-    specs += ["poisson", "poisson_median", "poisson_mean", "poisson_wavelet"]
-    specs += ["quant_var3", "quant_median_var7", "quant_mean_var10"]
+    for noise in C.NOISE_ORDER:
+        if noise in ("bloom", "shader"):
+            continue                                    # no spec argument (minibatch.py:1485-1511): deterministic_specs / bloom fixture
+        for lvl in C.LEVELS.get(noise, [None]):
+            for den in ("", "_wavelet", "_gaus_blur", "_mean", "_median", "_bilateral"):
+                specs.append(noise + den + ("_var" + lvl if lvl else ""))
     return specs
 
 
@@ -108,6 +106,8 @@ def evaluate(img, spec, fields):
     """The oracle's result for one case.  `original_<denoise>` = retain_original followed by the post-denoise
     pass (lib/model/test.py:1602-1607, 1787-1831; minibatch.py:1636-1662); everything else is one closure."""
     from oracle import closures as C
+    if spec == "original":
+        return img.copy()
     if spec.startswith("original_"):
         return C.apply_denoise(img, spec[len("original_"):])
     return C.corrupt(img, spec, fields=fields)
@@ -127,9 +127,12 @@ def versions():
 
 
 def tolerance_class(spec):
-    """'exact' | 'lsb' (<= 1 LSB on a small fraction) | 'brownian' (<= 1 LSB mod 256 on <= 1e-4) | 'periodic'."""
+    """'exact' | 'lsb' (<= 1 LSB on a small fraction) | 'brownian' (<= 1 LSB mod 256 on <= 1e-4) | 'periodic' |
+    'brownian_lsb' (brownian field as above, then a float denoiser: checked stage by stage on the GPU)."""
     from oracle import closures as C
     noise, den, _ = C.ladder(spec)
+    if noise == "brownian" and den in FLOAT_DENOISERS:
+        return "brownian_lsb"
     if den in FLOAT_DENOISERS or (spec.startswith("original_") and spec[len("original_"):] in FLOAT_DENOISERS):
         return "lsb"
     if noise == "brownian":

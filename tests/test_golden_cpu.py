@@ -28,6 +28,15 @@ def test_manifest_covers_every_case(manifest):
         assert any(s.startswith(noise) for s in specs), noise
     for den in ("gaus_blur", "mean", "median", "bilateral", "wavelet"):
         assert any(("_" + den) in s for s in specs), den
+    # the whole ladder, no cell skipped: noise x {none, 5 denoisers} x its three levels
+    from oracle import closures as C
+    for name in G.inputs():
+        have = {cid.split("|")[1] for cid in ids if cid.startswith(name + "|")}
+        for noise in C.NOISE_ORDER[:10]:
+            for lvl in C.LEVELS.get(noise, [None]):
+                for den in ("", "_wavelet", "_gaus_blur", "_mean", "_median", "_bilateral"):
+                    assert noise + den + ("_var" + lvl if lvl else "") in have, (name, noise, den, lvl)
+    assert len(ids) >= 330
 
 
 def test_oracle_reproduces_manifest(manifest):

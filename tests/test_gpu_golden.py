@@ -21,50 +21,80 @@ def _fields_to_dev(fields, cuda):
     return (torch.from_numpy(np.ascontiguousarray(v)[None]).to(cuda).contiguous(), None)
 
 
+def _lsb_ok(cid, spec, got, want):
+    """<= 1 LSB, on a bounded fraction of the pixels.  wavelet: the reference truncates a float64 that sits on
+    integers for block-constant areas (see tests/test_gpu_wavelet.py::check), so only the magnitude is tight there;
+    bilateral: < 0.2 % of pixels.  Natural image + wavelet WITHOUT noise in front: the reference's
+    sigma = median(|dd_1| != 0) counts float64 rounding-noise coefficients (|d| ~ 1e-17 where the pixel differences
+    cancel algebraically; 8-12 % of the non-zero chroma coefficients of this crop) as non-zero, and at one level
+    BayesShrink's dd threshold var / sqrt(dvar - var) sits 5 % from its pole: which of those coefficients cancel exactly
+    is decided by the last bit of float64 arithmetic, no fp32 path reproduces it, and the threshold moves by ~10 %
+    (DESIGN.md section 4).  Allowed there: <= 2 LSB, > 1 LSB on < 1 % of the pixels."""
+    a = np.abs(got.astype(int) - want.astype(int))
+    frac = 0.3 if "wavelet" in spec else 2e-3
+    if "wavelet" in spec and cid.startswith("natural"):
+        ok = a.max() <= 2 and (a > 1).mean() < 1e-2 and (a > 0).mean() < frac
+    else:
+        ok = a.max() <= 1 and (a > 0).mean() < frac
+    return ok, (cid, int(a.max()), float((a > 0).mean()), float((a > 1).mean()))
+
+
 def test_cuda_path_matches_golden_manifest(cuda):
+    """Every cell of the reference's ladder (10 noises x {none, 5 denoisers} x 3 levels, original_*, shader) on three
+    inputs, the draws of RandomState(3) injected: 525 cases, none skipped."""
     from image_denoising_b200 import api
+    from oracle import closures as C
     with open(G.MANIFEST) as f:
         manifest = json.load(f)
     same_libs = G.versions() == manifest["versions"]
     n_exact = n_tol = 0
     failures = []
+
+    def run(img, spec, fields):
+        return api.apply(torch.from_numpy(img[None]).to(cuda), spec, fields=_fields_to_dev(fields, cuda)).cpu().numpy()[0]
+
+    seen = set()
     for cid, img, spec, fields in G.cases():
         entry = manifest["cases"][cid]
-        got = api.apply(torch.from_numpy(img[None]).to(cuda), spec, fields=_fields_to_dev(fields, cuda)).cpu().numpy()[0]
+        seen.add(cid)
+        got = run(img, spec, fields)
         if entry["class"] == "exact":
-            assert G.digest(got) == entry["sha256"], cid
+            if G.digest(got) != entry["sha256"]:
+                failures.append((cid, "digest"))
             n_exact += 1
             continue
         want = G.evaluate(img, spec, fields)
-        if same_libs:
-            assert G.digest(want) == entry["sha256"], ("oracle drifted from the manifest", cid)
+        if same_libs and G.digest(want) != entry["sha256"]:
+            failures.append((cid, "oracle drifted from the manifest"))
         d = (got.astype(int) - want.astype(int))
         if entry["class"] == "lsb":
-            # wavelet: the reference truncates a float64 that sits on integers for block-constant areas (see
-            # tests/test_gpu_wavelet.py::check), so only the magnitude is tight there; bilateral: < 0.2 % of pixels.
-            # Natural image + wavelet: the reference's sigma = median(|dd_1| != 0) counts float64 rounding-noise
-            # coefficients (|d| ~ 1e-17 where the pixel differences cancel algebraically; 8-12 % of the non-zero
-            # chroma coefficients of this crop) as non-zero, and at one level BayesShrink's dd threshold
-            # var / sqrt(dvar - var) sits 5 % from its pole: which of those coefficients cancel exactly is decided by
-            # the last bit of float64 arithmetic, no fp32 path reproduces it, and the threshold moves by ~10 %
-            # (DESIGN.md section 4).  Allowed there: <= 2 LSB, > 1 LSB on < 1 % of the pixels.
-            frac = 0.3 if "wavelet" in spec else 2e-3
-            a = np.abs(d)
-            if "wavelet" in spec and cid.startswith("natural"):
-                ok = a.max() <= 2 and (a > 1).mean() < 1e-2 and (a > 0).mean() < frac
-            else:
-                ok = a.max() <= 1 and (a > 0).mean() < frac
+            ok, info = _lsb_ok(cid, spec, got, want)
             if not ok:
-                failures.append((cid, int(a.max()), float((a > 0).mean()), float((a > 1).mean())))
+                failures.append(info)
         elif entry["class"] == "brownian":
             m = d % 256
             bad = m != 0
             if spec.count("_") == 1:                      # noise only: +-1 mod 256 on <= 1e-4 of the elements
-                assert np.all((m[bad] == 1) | (m[bad] == 255)) and bad.mean() <= 1e-4, (cid, int(bad.sum()))
-            else:
-                assert bad.mean() <= 1e-4, (cid, int(bad.sum()))
+                if not (np.all((m[bad] == 1) | (m[bad] == 255)) and bad.mean() <= 1e-4):
+                    failures.append((cid, int(bad.sum())))
+            elif bad.mean() > 9e-4:                       # 3 x 3 filters spread one element over 9 outputs
+                failures.append((cid, int(bad.sum())))
+        elif entry["class"] == "brownian_lsb":
+            # stage by stage: the CUDA field (held to the brownian allowance by the noise-only case of the same level)
+            # goes through the ORACLE's denoiser; the fused CUDA result must be within 1 LSB of that
+            noise, den, level = C.ladder(spec)
+            noised = run(img, "brownian_var" + level, fields)
+            ok, info = _lsb_ok(cid, spec, got, C.apply_denoise(noised, den))
+            if not ok:
+                failures.append(info)
+            dn = (noised.astype(int) - C.apply_noise(img, noise, level, fields).astype(int)) % 256
+            if (dn != 0).mean() > 1e-4:
+                failures.append((cid, "brownian field", int((dn != 0).sum())))
         else:                                             # periodic: last-ulp differences of fp64 sin
-            assert (d != 0).mean() <= 1e-5, (cid, int((d != 0).sum()))
+            lim = 1e-5 if spec.count("_") == 1 else 9e-5
+            if (d != 0).mean() > lim:
+                failures.append((cid, int((d != 0).sum())))
         n_tol += 1
     assert not failures, failures
-    assert n_exact >= 170 and n_tol >= 90
+    assert seen == set(manifest["cases"]), "manifest and case list differ"
+    assert n_exact + n_tol >= 520 and n_exact >= 250

@@ -103,7 +103,7 @@ def test_haar_fast_path_equals_general_path(cuda, tmp_path):
     for tag, env in (("fast", {}), ("general", {"B2D_HAAR": "0"})):
         path = str(tmp_path / (tag + ".npz"))
         subprocess.run([sys.executable, "-c", _HAAR_SCRIPT, root, path] + _HAAR_SPECS, check=True,
-                       env=dict(os.environ, **env), timeout=600)
+                       env=dict(os.environ, B2D_DEBUG_KNOBS="1", **env), timeout=600)
         outs[tag] = dict(np.load(path))
     assert set(outs["fast"]) == set(outs["general"]) and len(outs["fast"]) == 2 * len(_HAAR_SPECS), sorted(outs["fast"])
     for key, a in outs["fast"].items():
@@ -137,7 +137,7 @@ np.savez(sys.argv[2], **out)
     for tag, env in (("fast", {"B2D_HAAR": "0"}), ("unfused", {"B2D_HAAR": "0", "B2D_WV_FUSED": "0"}),
                      ("generic", {"B2D_HAAR": "0", "B2D_WV_GENERIC": "1"})):
         path = str(tmp_path / (tag + ".npz"))
-        subprocess.run([sys.executable, "-c", script, root, path], check=True, env=dict(os.environ, **env), timeout=600)
+        subprocess.run([sys.executable, "-c", script, root, path], check=True, env=dict(os.environ, B2D_DEBUG_KNOBS="1", **env), timeout=600)
         outs[tag] = dict(np.load(path))
     assert set(outs["fast"]) == set(outs["generic"]) and len(outs["fast"]) == 16
     for tag in ("fast", "unfused"):                              # fast = the fused 2-D kernels (rows + columns + energies)

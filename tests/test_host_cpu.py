@@ -91,6 +91,38 @@ def test_mix_resolution_uses_the_reference_lists():
     assert spec.resolve_mix("sap_mean_var0.4") == "sap_mean_var0.4"
 
 
+def test_mix_with_a_denoiser_keeps_the_denoiser():
+    """`noise_mix_var_*_<denoise>`: the reference picks a noise-only closure and denoises in its post-denoise pass
+    (minibatch.py:1636-1663; test.py:1787-1819 keeps only `wavelet` live, :1805-1812).  resolve() returns both parts."""
+    r = random.Random(5)
+    for den in ("gaus_blur", "mean", "median", "wavelet", "bilateral"):
+        concrete, post = spec.resolve("noise_mix_var_low_" + den, "train", r)
+        assert concrete in spec.MIX_LISTS["train"]["var_low"] and post == den
+        assert spec.parse(concrete).denoise == "none"
+        concrete, post = spec.resolve("noise_mix_var_low_" + den, "test", r)
+        assert concrete in spec.MIX_LISTS["test"]["var_low"] and post == ("wavelet" if den == "wavelet" else None)
+    assert spec.resolve("noise_mix_var_high", "train", r)[1] is None
+    # elif order of the post pass: gaus_blur before mean before median before wavelet before bilateral
+    assert spec.post_denoiser("noise_mix_var_low_wavelet_mean", "train") == "mean"
+    assert spec.post_denoiser("noise_mix_var_low_wavelet_mean", "test") is None        # `mean` branch only prints
+    # a concrete spec is one closure call: nothing is added
+    assert spec.resolve("sap_mean_var0.4", "train") == ("sap_mean_var0.4", None)
+
+
+def test_q3_gaussian_random_level_is_opt_in():
+    """Quirk Q3 (minibatch.py:1575-1580, test.py:1678-1682): `gaussian` specs ignore their own level and denoiser."""
+    assert spec.resolve("gaussian_median_var1.5", "train", random.Random(0)) == ("gaussian_median_var1.5", None)
+    got = set()
+    for i in range(200):
+        concrete, post = spec.resolve("gaussian_median_var1.5", "train", random.Random(i), spec.COMPAT_GAUSSIAN_RANDOM_LEVEL)
+        assert post == "median" and spec.parse(concrete).denoise == "none"
+        got.add(concrete)
+    assert got == {"gaussian_var0.1", "gaussian_var1.0", "gaussian_var1.5"}
+    assert spec.resolve("gaussian_median_var1.5", "test", random.Random(0), spec.COMPAT_GAUSSIAN_RANDOM_LEVEL)[1] is None
+    assert spec.resolve("sap_var0.4", "test", None, spec.COMPAT_GAUSSIAN_RANDOM_LEVEL) == ("sap_var0.4", None)
+    assert _lib.COMPAT_GAUSSIAN_RANDOM_LEVEL == 16 and _lib.COMPAT_SAP_TRAIN06 == 2
+
+
 def test_plan_create_fails_loudly_without_gpu():
     import torch
     if torch.cuda.is_available():
