@@ -43,7 +43,7 @@ class B2DError(RuntimeError):
 
 
 EXPORTS = ["b2d_parse_spec", "b2d_plan_create", "b2d_plan_workspace_bytes", "b2d_plan_destroy", "b2d_run",
-           "b2d_run_host", "b2d_host_register", "b2d_host_unregister", "b2d_noise_field", "b2d_stats", "b2d_lab_convert",
+           "b2d_run_host", "b2d_host_register", "b2d_host_unregister", "b2d_noise_field", "b2d_wavelet_stats", "b2d_stats", "b2d_lab_convert",
            "b2d_poisson_table", "b2d_gamma_table", "b2d_blob_shape", "b2d_blob_prep", "b2d_jpeg_info", "b2d_jpeg_create", "b2d_jpeg_decode", "b2d_jpeg_destroy", "b2d_jpeg_entropy", "b2d_nms", "b2d_nms_workspace_bytes", "b2d_nms_device",
            "b2d_launch_count", "b2d_reset_launch_count", "b2d_last_error", "b2d_version"]
 
@@ -83,6 +83,7 @@ def lib():
     L.b2d_host_unregister.argtypes = [vp]
     L.b2d_noise_field.argtypes = [vp, vp, vp, u64, u64, vp]
     L.b2d_stats.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.b2d_wavelet_stats.argtypes = [vp, ctypes.c_int, vp, vp]
     L.b2d_lab_convert.argtypes = [vp, vp, sz, ctypes.c_int, vp]
     L.b2d_poisson_table.argtypes = [ctypes.c_int, vp]
     L.b2d_gamma_table.argtypes = [ctypes.c_double, vp, vp, vp]
@@ -108,8 +109,8 @@ def lib():
     L.b2d_last_error.restype = ctypes.c_char_p
     L.b2d_version.restype = ctypes.c_char_p
     for name in ("b2d_parse_spec", "b2d_plan_create", "b2d_plan_workspace_bytes", "b2d_run", "b2d_run_host",
-                 "b2d_host_register", "b2d_host_unregister", "b2d_noise_field", "b2d_stats", "b2d_lab_convert",
-                 "b2d_poisson_table", "b2d_gamma_table", "b2d_blob_shape", "b2d_blob_prep", "b2d_jpeg_info", "b2d_jpeg_create",
+                 "b2d_host_register", "b2d_host_unregister", "b2d_noise_field", "b2d_wavelet_stats", "b2d_stats",
+                 "b2d_lab_convert", "b2d_poisson_table", "b2d_gamma_table", "b2d_blob_shape", "b2d_blob_prep", "b2d_jpeg_info", "b2d_jpeg_create",
                  "b2d_jpeg_decode"):
         getattr(L, name).restype = ctypes.c_int
     _lib = L

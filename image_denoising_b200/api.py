@@ -105,6 +105,14 @@ class Plan:
                                               int(seed) & (2 ** 64 - 1), int(first_index), stream))
         return f0, f1
 
+    def wavelet_stats(self, image=0):
+        """Test hook (b2d_wavelet_stats): (3, 4) float32 array, per "YCbCr" channel {sigma, min, max, count}
+        of image `image` (position in its spec group) as the LAST run left them."""
+        out = np.zeros((3, 4), np.float32)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(_lib.lib().b2d_wavelet_stats(self._h, int(image), out.ctypes.data, stream))
+        return out
+
     def stats(self, out, ref=None):
         """Per-image (checksum uint64 as int64 tensor, sse float64 or None)."""
         self._check(out, "out")

@@ -415,6 +415,7 @@ int run_haar(const b2d_plan& p, const ImageSet& s, int kind, const NoiseArgs& na
     wavelet_sigma_thresholds(g, dd1, stats, hist, cnt * 3, st);
     rc = dispatch_haar(kind, 1, grid, st, s, na, hg, dd1, stats, fa, first);
     if (rc) return rc;
+    p.wv_stats_dev = stats; p.wv_stats_first = first; p.wv_stats_count = cnt;
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail_cuda(e, "haar wavelet launch");
   }

@@ -57,6 +57,9 @@ struct b2d_plan {
   size_t ws_bytes, off_par, off_bitmap, off_stage, off_aux, off_scan, off_denoise, off_pix;
   uint32_t brown_chunks;
   bool need_aux;
+  // test hook b2d_wavelet_stats: where the last wavelet chunk of the last run left its statistics
+  mutable const void* wv_stats_dev;   // WvStats[3 * wv_stats_count] on the device
+  mutable int wv_stats_first, wv_stats_count;   // group-relative index of the chunk's first image, images in it
   // b2d_run_host resources (lazily created)
   uint8_t *h_d_in, *h_d_out, *h_d_ws;
   cudaStream_t h_streams[3];

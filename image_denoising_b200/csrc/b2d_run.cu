@@ -76,6 +76,8 @@ extern "C" int b2d_plan_create(b2d_plan** out, int device, int n, int h, int w, 
   p->d_poisson = nullptr;
   p->h_ready = false;
   p->need_aux = false;
+  p->wv_stats_dev = nullptr;
+  p->wv_stats_first = p->wv_stats_count = 0;
   // group images by identical spec, keeping first-appearance order
   for (int i = 0; i < n; ++i) {
     const b2d_spec& s = specs[n_specs == 1 ? 0 : i];

@@ -992,6 +992,7 @@ int run_wavelet(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, int ki
     }
     k_wv_final<<<dim3(blocks(((size_t)p.h * p.w + 3) / 4), 1, cnt), 256, 0, st>>>(s, g, ws, stats, fa, first);
     count_launch();
+    p.wv_stats_dev = stats; p.wv_stats_first = first; p.wv_stats_count = cnt;
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail_cuda(e, "wavelet launch");
   }
@@ -999,3 +1000,30 @@ int run_wavelet(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, int ki
 }
 
 }  // namespace b2d
+
+// Test hook: sigma / clip range / dd_1 threshold the last b2d_run left for one image of the last wavelet chunk.
+extern "C" int b2d_wavelet_stats(const b2d_plan* plan, int image_in_group, float* h_out, void* cuda_stream) {
+  using namespace b2d;
+  if (!plan || !h_out) return fail(B2D_ERR_INVALID, "b2d_wavelet_stats: null argument");
+  if (!plan->wv_stats_dev) return fail(B2D_ERR_INVALID, "b2d_wavelet_stats: no wavelet run on this plan yet");
+  const int k = image_in_group - plan->wv_stats_first;
+  if (k < 0 || k >= plan->wv_stats_count)
+    return fail(B2D_ERR_INVALID, "b2d_wavelet_stats: image %d is not in the last chunk [%d, %d)", image_in_group,
+                plan->wv_stats_first, plan->wv_stats_first + plan->wv_stats_count);
+  DeviceGuard guard(plan->device);
+  if (!guard.ok()) return fail_cuda(guard.err, "cudaSetDevice");
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  WvStats hs[3];
+  cudaError_t e = cudaMemcpyAsync(hs, static_cast<const WvStats*>(plan->wv_stats_dev) + (size_t)k * 3, sizeof(hs),
+                                  cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) return fail_cuda(e, "b2d_wavelet_stats");
+  for (int c = 0; c < 3; ++c) {
+    h_out[4 * c + 0] = hs[c].sigma;
+    h_out[4 * c + 1] = hs[c].lo;
+    h_out[4 * c + 2] = hs[c].hi;
+    h_out[4 * c + 3] = (float)hs[c].count;
+  }
+  return B2D_OK;
+}
+

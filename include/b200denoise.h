@@ -166,6 +166,16 @@ int b2d_host_unregister(void* ptr);
 int b2d_noise_field(b2d_plan* plan, float* d_f0, float* d_f1, uint64_t seed,
                     uint64_t first_global_image_index, void* cuda_stream);
 
+/* Test hook: the per-channel statistics the wavelet denoiser derived for one image during the LAST b2d_run of this
+ * plan (skimage _wavelet_threshold / _sigma_est_dwt, reached from lib/roi_data_layer/minibatch.py:92-94).
+ * image_in_group = position of the image inside its spec group (= batch index when the plan has one spec); it must
+ * lie in the last workspace chunk the run processed (small test batches are one chunk).  h_out[12] = for each of the
+ * three "YCbCr" channels {sigma, min, max, count}: sigma = median(|dd_1| != 0) / 0.6745 in the channel's OWN units
+ * (divide by max - min for skimage's normalised value), min / max = the channel range used for the normalisation and
+ * the inner clip, count = how many dd_1 coefficients were non-zero.  Synchronises cuda_stream.  The parity tests use it
+ * to hand the oracle the same exact-zero census (tests/test_gpu_wavelet.py). */
+int b2d_wavelet_stats(const b2d_plan* plan, int image_in_group, float* h_out, void* cuda_stream);
+
 /* Test hook: the uint8 colour conversions of the `quant` branch alone, on n_pixels interleaved
  * 3-byte pixels (device pointers): direction 0 = cv2.cvtColor(COLOR_BGR2LAB), 1 = COLOR_LAB2BGR
  * (lib/roi_data_layer/minibatch.py:496,507). */

@@ -98,13 +98,19 @@ def apply_denoise(x, denoise, wavelet="bior1.5", wavelet_levels=None, median_k=3
     raise ValueError(denoise)
 
 
-def corrupt(img, spec, fields=None, rng=np.random, wavelet="bior1.5",
-            wavelet_levels=None, median_k=3):
-    """One closure call: uint8 BGR in -> uint8 out (test.py semantics)."""
+def noise_stage(img, spec, fields=None, rng=np.random):
+    """What the closure hands to its denoiser: float64 for the float noises, uint8 otherwise."""
     noise, denoise, level = ladder(spec)
     if noise in LEVELS and level is None:
         raise UnboundLocalError("unknown level in %r (test.py leaves `im` unbound)" % spec)
     x = apply_noise(img, noise, level, fields, rng)
     if noise == "poisson" and denoise == "wavelet":
         x = N.to_u8(x)                                  # minibatch.py:212-213
-    return apply_denoise(x, denoise, wavelet, wavelet_levels, median_k)
+    return x
+
+
+def corrupt(img, spec, fields=None, rng=np.random, wavelet="bior1.5",
+            wavelet_levels=None, median_k=3):
+    """One closure call: uint8 BGR in -> uint8 out (test.py semantics)."""
+    denoise = ladder(spec)[1]
+    return apply_denoise(noise_stage(img, spec, fields, rng), denoise, wavelet, wavelet_levels, median_k)

@@ -151,14 +151,17 @@ def auto_levels(shape, wavelet):
     return max(lv - 3, 1)
 
 
-def wavelet_threshold(image, wavelet="db1", wavelet_levels=None, return_stats=False):
-    """_wavelet_threshold(image, wavelet, method='BayesShrink', mode='soft')."""
+def wavelet_threshold(image, wavelet="db1", wavelet_levels=None, return_stats=False, sigma=None):
+    """_wavelet_threshold(image, wavelet, method='BayesShrink', mode='soft').
+    ``sigma`` (tests only): use this noise estimate instead of _sigma_est_dwt's - the stage-wise parity
+    check hands the oracle the estimate the CUDA path derived (see sigma_census)."""
     original_extent = tuple(slice(s) for s in image.shape)
     if wavelet_levels is None:
         wavelet_levels = auto_levels(image.shape, wavelet)
     coeffs = wavedec2(image, wavelet, wavelet_levels)
     dcoeffs = coeffs[1:]
-    sigma = sigma_est_dwt(dcoeffs[-1]["dd"])
+    if sigma is None:
+        sigma = sigma_est_dwt(dcoeffs[-1]["dd"])
     var = sigma ** 2
     threshold = [{key: bayes_thresh(level[key], var) for key in level} for level in dcoeffs]
     denoised_detail = [{key: soft_threshold(level[key], thresh[key]) for key in level}
@@ -192,7 +195,77 @@ def ycbcr2rgb(ycbcr):
     return np.dot(arr, RGB_FROM_YCBCR.T.copy())
 
 
-def denoise_wavelet(image, wavelet="db1", wavelet_levels=None, return_stats=False):
+def _hh2(x):
+    """2 x 2 differences d - c - b + a of the symmetric-extended plane, sampled the way both wavelets'
+    high-pass filters ([-s, s] at taps 4, 5 of bior1.5 = the two taps of db1) sample them: the integer
+    skeleton of the finest 'dd' band.  Returns (a, b, c, d) planes of the band's shape."""
+    F = 2
+    p = np.pad(x, ((F - 1, F - 1), (F - 1, F - 1)), mode="symmetric")
+    m0, m1 = (x.shape[0] + F - 1) // 2, (x.shape[1] + F - 1) // 2
+    r0, r1 = p[1:1 + 2 * m0:2], p[2:2 + 2 * m0:2]
+    return r0[:, 1:1 + 2 * m1:2], r0[:, 2:2 + 2 * m1:2], r1[:, 1:1 + 2 * m1:2], r1[:, 2:2 + 2 * m1:2]
+
+
+def sigma_census(image, wavelet="db1", tiny=1e-6):
+    """For each "YCbCr" channel of ``image``: what _sigma_est_dwt's result can be when the set of EXACTLY-zero
+    finest 'dd' coefficients is decided by an arithmetic other than this float64 one.
+
+    sigma = median(|dd_1|[dd_1 != 0]) / 0.6745 filters exact zeros.  dd_1 of both wavelets is a 2 x 2 difference
+    (a - b) - (c - d) of channel samples.  When it cancels ALGEBRAICALLY but the four samples are not pairwise
+    equal, the computed value is 0.0 or rounding noise (|d| ~ 1e-17 in float64, ~1e-8 in float32) depending on
+    the last bit of the colour matrix product and the normalisation - BLAS build, float width, operation order:
+    those coefficients are AMBIGUOUS, and counting k of them as non-zero shifts the rank of the median.
+    uint8-valued images (s&p, poisson, quant, brownian, periodic, clean): decided exactly in integers
+    (1000 x the BT.601 matrix is integral).  Float images: a coefficient is ambiguous when it is below ``tiny``
+    of the channel range in the normalised or the un-normalised float64 evaluation.
+    Returns a list of (sigma_min, sigma_max, n_sure, n_ambiguous): the estimates with all / none of the ambiguous
+    coefficients counted.  A well-conditioned channel has n_ambiguous == 0 and sigma_min == sigma_max == the
+    oracle's sigma."""
+    if image.dtype == np.uint8:
+        image = image.astype(np.float64) / 255.0
+    image = np.asarray(image, np.float64)
+    as_int = np.rint(image * 255.0)
+    integral = bool(np.all(np.abs(image * 255.0 - as_int) < 1e-9))
+    ycc = rgb2ycbcr(image)
+    m1000 = np.rint(YCBCR_FROM_RGB * 1000.0).astype(np.int64)
+    out = []
+    for i in range(3):
+        ch = ycc[..., i]
+        mn, mx = ch.min(), ch.max()
+        norm = (ch - mn) / (mx - mn)
+        dd = np.abs(dwt_axis(dwt_axis(norm, wavelet, 0)[1], wavelet, 1)[1])
+        F = len(WAVELETS[wavelet][0])
+        if integral:
+            yi = as_int.astype(np.int64) @ m1000[i]                # exact, up to the common factor 1 / 255000
+            ids = np.arange(yi.size, dtype=np.int64).reshape(yi.shape)
+            m0, m1 = dd.shape
+
+            def quad(plane):                                       # taps 4 (-s) and 5 (+s) of bior1.5 = the two taps of db1
+                p = np.pad(plane, ((F - 1, F - 1), (F - 1, F - 1)), mode="symmetric")
+                ra, rb = p[F - (F // 2 - 1):F - (F // 2 - 1) + 2 * m0:2], p[F - F // 2:F - F // 2 + 2 * m0:2]
+                return (ra[:, F - (F // 2 - 1):F - (F // 2 - 1) + 2 * m1:2], rb[:, F - (F // 2 - 1):F - (F // 2 - 1) + 2 * m1:2],
+                        ra[:, F - F // 2:F - F // 2 + 2 * m1:2], rb[:, F - F // 2:F - F // 2 + 2 * m1:2])
+            a, b, c, d = quad(yi)
+            ia, ib, ic, id_ = quad(ids)
+            alg_zero = (a - b - c + d) == 0
+            # the same ARRAY ELEMENT on both sides (duplicated border samples): zero in every arithmetic
+            zero = ((ia == ib) & (ic == id_)) | ((ia == ic) & (ib == id_))
+            amb = alg_zero & ~zero
+        else:
+            ddu = np.abs(dwt_axis(dwt_axis(ch, wavelet, 0)[1], wavelet, 1)[1]) / (mx - mn)
+            zero = (dd == 0.0) & (ddu == 0.0)
+            amb = ~zero & (np.minimum(dd, ddu) <= tiny)
+        sure = np.sort(dd[~amb & ~zero].ravel())
+        k = int(amb.sum())
+        if sure.size == 0:
+            out.append((0.0, 0.0, 0, k))
+            continue
+        with_all = np.concatenate([np.zeros(k), sure])          # ambiguous ones counted (as ~0 values)
+        out.append((float(np.median(with_all)) / NORM_PPF_075, float(np.median(sure)) / NORM_PPF_075, int(sure.size), k))
+    return out
+
+
+def denoise_wavelet(image, wavelet="db1", wavelet_levels=None, return_stats=False, sigmas=None):
     """denoise_wavelet(image, method='BayesShrink', mode='soft', wavelet=...,
     wavelet_levels=..., multichannel=True, convert2ycbcr=True)
     (minibatch.py:92-94).  ``image``: uint8 or float64 HxWx3 in the array's own
@@ -207,7 +280,8 @@ def denoise_wavelet(image, wavelet="db1", wavelet_levels=None, return_stats=Fals
         channel = out[..., i] - mn
         with np.errstate(divide="ignore", invalid="ignore"):
             channel /= mx - mn
-        res = wavelet_threshold(channel, wavelet, wavelet_levels, return_stats)
+        res = wavelet_threshold(channel, wavelet, wavelet_levels, return_stats,
+                                None if sigmas is None else float(sigmas[i]))
         if return_stats:
             res, st = res
             st.update(min=mn, max=mx)

@@ -8,58 +8,63 @@ import torch
 
 from conftest import synth_batch
 from oracle import closures as C
+import wavelet_check as WC
 
 pytestmark = pytest.mark.gpu
 
 
-def check(got, want, frac=0.3):
-    """<= 1 LSB everywhere.  The fraction of 1-LSB differences is only loosely bounded: with db1 and
-    few levels whole 2x2 blocks collapse to their mean, a multiple of 1/4 grey level, so 255*out sits
-    EXACTLY on an integer for a quarter of the pixels and the reference's truncation of its float64
-    result (143.99999999999997 vs 144.0) is decided by rounding noise no fp32 path can reproduce."""
-    d = np.abs(got.astype(int) - want.astype(int))
-    assert d.max() <= 1, (d.max(), (d > 1).sum())
-    assert (d > 0).mean() < frac, (d > 0).mean()
+def _plan_run(cuda, batch, spec, fields=None, **kw):
+    """One plan for the whole batch (so the statistics hook sees the run); returns (plan, uint8 results)."""
+    from image_denoising_b200 import api
+    n, h, w, _ = batch.shape
+    plan = api.get_plan(n, h, w, spec, cuda.index, **kw)
+    return plan, plan.run(torch.from_numpy(batch).to(cuda), fields=fields).cpu().numpy()
+
+
+def _assert_stagewise(plan, got, xs, wavelet, levels, tag):
+    """tests/wavelet_check.py: sigma of every image inside the oracle's census range (one value when no dd_1
+    coefficient is ambiguous), then <= 1 LSB everywhere against the oracle evaluated with that sigma, and < 2 % of
+    the pixels that are not sitting on an integer."""
+    fails = []
+    for i, x in enumerate(xs):
+        fails += WC.stagewise(got[i], x, plan.wavelet_stats(i), wavelet, levels or None, "%s[%d]" % (tag, i))
+    assert not fails, fails
 
 
 @pytest.mark.parametrize("shape", [(64, 96), (375, 500), (37, 53), (120, 200)])
 @pytest.mark.parametrize("wl", [("bior1.5", 0), ("db1", 3), ("db1", 0)])
 def test_wavelet_on_clean_uint8(cuda, shape, wl):
-    from image_denoising_b200 import api
     batch = synth_batch(2, shape[0], shape[1], seed=31, kind="smooth")
-    got = api.apply(torch.from_numpy(batch).to(cuda), "original_wavelet", wavelet=wl[0], levels=wl[1]).cpu().numpy()
-    for i in range(2):
-        want = C.apply_denoise(batch[i], "wavelet", wavelet=wl[0], wavelet_levels=wl[1] or None)
-        check(got[i], want, 2e-2 if wl[0] == "bior1.5" else 0.3)
+    plan, got = _plan_run(cuda, batch, "original_wavelet", wavelet=wl[0], levels=wl[1])
+    _assert_stagewise(plan, got, list(batch), wl[0], wl[1], "original_wavelet")
 
 
 @pytest.mark.parametrize("noise", ["gaussian", "speckle", "sap", "uniform", "gamma", "rayleigh", "poisson", "brownian"])
 @pytest.mark.parametrize("wl", [("bior1.5", 0), ("db1", 3)])
 def test_noise_wavelet_closure_injected(cuda, noise, wl):
     """Whole closure: injected noise field -> (float) -> denoise_wavelet -> ->u8."""
-    from image_denoising_b200 import api
     from test_gpu_noise import LEVEL, draw_fields, to_dev
     h, w = 96, 160
     batch = synth_batch(2, h, w, seed=17, kind="smooth")
     rng = np.random.RandomState(3)
     spec = noise + "_wavelet" + ("_var" + LEVEL[noise] if noise in LEVEL else "")
     fields = [draw_fields(noise, LEVEL.get(noise), (h, w, 3), rng, im) for im in batch]
-    got = api.apply(torch.from_numpy(batch).to(cuda), spec, fields=to_dev(fields, noise, cuda), wavelet=wl[0],
-                    levels=wl[1]).cpu().numpy()
-    for i in range(2):
-        want = C.corrupt(batch[i], spec, fields=fields[i], wavelet=wl[0], wavelet_levels=wl[1] or None)
-        check(got[i], want)
+    plan, got = _plan_run(cuda, batch, spec, fields=to_dev(fields, noise, cuda), wavelet=wl[0], levels=wl[1])
+    if noise == "brownian":          # the parallel fp64 scan differs from cumsum by 1 LSB mod 256 on <= 1e-4 of the field:
+        from image_denoising_b200 import api         # feed the oracle's denoiser the CUDA field (checked in test_gpu_noise)
+        xs = list(api.apply(torch.from_numpy(batch).to(cuda), "brownian_var" + LEVEL[noise], fields=to_dev(fields, noise, cuda)).cpu().numpy())
+    else:
+        xs = [C.noise_stage(batch[i], spec, fields=fields[i]) for i in range(2)]
+    _assert_stagewise(plan, got, xs, wl[0], wl[1], spec)
 
 
 def test_periodic_wavelet_and_large(cuda):
-    from image_denoising_b200 import api
     batch = synth_batch(1, 600, 1000, seed=3, kind="smooth")
     for spec, kw in (("periodic_wavelet_var100", {}), ("original_wavelet", {"wavelet": "db1", "levels": 3})):
-        got = api.apply(torch.from_numpy(batch).to(cuda), spec, **kw).cpu().numpy()
+        plan, got = _plan_run(cuda, batch, spec, **kw)
         wl, lv = kw.get("wavelet", "bior1.5"), kw.get("levels") or None
-        want = (C.apply_denoise(batch[0], "wavelet", wl, lv) if spec.startswith("original")
-                else C.corrupt(batch[0], spec, wavelet=wl, wavelet_levels=lv))
-        check(got[0], want)
+        x = batch[0] if spec.startswith("original") else C.noise_stage(batch[0], spec)
+        _assert_stagewise(plan, got, [x], wl, lv, spec)
 
 
 def test_generator_mode_denoises(cuda):
