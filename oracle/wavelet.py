@@ -235,25 +235,25 @@ def sigma_census(image, wavelet="db1", tiny=1e-6):
         norm = (ch - mn) / (mx - mn)
         dd = np.abs(dwt_axis(dwt_axis(norm, wavelet, 0)[1], wavelet, 1)[1])
         F = len(WAVELETS[wavelet][0])
+        ids = np.arange(ch.size, dtype=np.int64).reshape(ch.shape)
+        m0, m1 = dd.shape
+
+        def quad(plane):                                           # taps F/2-1 (-s) and F/2 (+s): bior1.5's 4, 5 = db1's 0, 1
+            p = np.pad(plane, ((F - 1, F - 1), (F - 1, F - 1)), mode="symmetric")
+            o4, o5 = F - (F // 2 - 1), F - F // 2
+            ra, rb = p[o4:o4 + 2 * m0:2], p[o5:o5 + 2 * m0:2]
+            return ra[:, o4:o4 + 2 * m1:2], rb[:, o4:o4 + 2 * m1:2], ra[:, o5:o5 + 2 * m1:2], rb[:, o5:o5 + 2 * m1:2]
+        ia, ib, ic, id_ = quad(ids)
+        # the same ARRAY ELEMENT on both sides (duplicated border samples): zero in every arithmetic
+        zero = ((ia == ib) & (ic == id_)) | ((ia == ic) & (ib == id_))
         if integral:
             yi = as_int.astype(np.int64) @ m1000[i]                # exact, up to the common factor 1 / 255000
-            ids = np.arange(yi.size, dtype=np.int64).reshape(yi.shape)
-            m0, m1 = dd.shape
-
-            def quad(plane):                                       # taps 4 (-s) and 5 (+s) of bior1.5 = the two taps of db1
-                p = np.pad(plane, ((F - 1, F - 1), (F - 1, F - 1)), mode="symmetric")
-                ra, rb = p[F - (F // 2 - 1):F - (F // 2 - 1) + 2 * m0:2], p[F - F // 2:F - F // 2 + 2 * m0:2]
-                return (ra[:, F - (F // 2 - 1):F - (F // 2 - 1) + 2 * m1:2], rb[:, F - (F // 2 - 1):F - (F // 2 - 1) + 2 * m1:2],
-                        ra[:, F - F // 2:F - F // 2 + 2 * m1:2], rb[:, F - F // 2:F - F // 2 + 2 * m1:2])
             a, b, c, d = quad(yi)
-            ia, ib, ic, id_ = quad(ids)
-            alg_zero = (a - b - c + d) == 0
-            # the same ARRAY ELEMENT on both sides (duplicated border samples): zero in every arithmetic
-            zero = ((ia == ib) & (ic == id_)) | ((ia == ic) & (ib == id_))
-            amb = alg_zero & ~zero
+            amb = ((a - b - c + d) == 0) & ~zero
         else:
+            # float image (clipped Gaussian / speckle ...): whatever is below `tiny` in the normalised or in the
+            # un-normalised float64 evaluation - exact float64 zeros of distinct samples included, they are luck
             ddu = np.abs(dwt_axis(dwt_axis(ch, wavelet, 0)[1], wavelet, 1)[1]) / (mx - mn)
-            zero = (dd == 0.0) & (ddu == 0.0)
             amb = ~zero & (np.minimum(dd, ddu) <= tiny)
         sure = np.sort(dd[~amb & ~zero].ravel())
         k = int(amb.sum())

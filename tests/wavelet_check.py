@@ -37,6 +37,8 @@ def stagewise(got, x, gpu_stats, wavelet="bior1.5", levels=None, tag=""):
         smin, smax, n_sure, n_amb = census[c]
         if not (smin * (1 - SIGMA_RTOL) - 1e-9 <= s_norm <= smax * (1 + SIGMA_RTOL) + 1e-9):
             fails.append((tag, "sigma outside the census range", c, s_norm, smin, smax, n_sure, n_amb))
+        if not (n_sure <= int(gpu_stats[c, 3]) <= n_sure + n_amb):
+            fails.append((tag, "non-zero dd_1 count outside the census", c, int(gpu_stats[c, 3]), n_sure, n_amb))
         sig.append(s_norm)
     f = 255.0 * W.denoise_wavelet(xf, wavelet, levels, sigmas=sig)
     want = f.astype(np.int32).astype(np.uint8)          # the reference's ->u8 (values are in [0, 255])
