@@ -103,9 +103,9 @@ static void host_draws(uint64_t seed, uint64_t gi, int h, int w, double* d /* [8
   const int nline = (w + 9) / 10;                         // range(0, W, 10)
   const int rad_hi = h / 100 - 2;                         // randint(1, H//100 - 2), validated >= 1
   for (int k = 0; k < BLOOM_RANDOM; ++k) {
-    const uint4 r0 = philox4x32_10((uint32_t)k, 0xB100u, (uint32_t)gi, (uint32_t)(gi >> 32), (uint32_t)seed,
+    const uint4 r0 = philox4x32((uint32_t)k, 0xB100u, (uint32_t)gi, (uint32_t)(gi >> 32), (uint32_t)seed,
                                    (uint32_t)(seed >> 32));
-    const uint4 r1 = philox4x32_10((uint32_t)k, 0xB101u, (uint32_t)gi, (uint32_t)(gi >> 32), (uint32_t)seed,
+    const uint4 r1 = philox4x32((uint32_t)k, 0xB101u, (uint32_t)gi, (uint32_t)(gi >> 32), (uint32_t)seed,
                                    (uint32_t)(seed >> 32));
     const double u = ((double)r0.x + 0.5) / 4294967296.0;
     const int idx = (int)(((uint64_t)r0.y * (uint64_t)nline) >> 32);

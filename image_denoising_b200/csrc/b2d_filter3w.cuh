@@ -83,20 +83,39 @@ struct Filter3W<FK_MEAN3, KW> {
       p.o[i] = r.ol(i + 1) + r.o[i + 1] + r.orr(i + 1);
     }
   }
-  // (S + 4) / 9 for S <= 2295 is bits 16..23 of (S + 4) * 7282 (exact: 9 * 7282 = 2^16 + 2 and
-  // 2299 * 2 < 2^16).  The four quotients are steered to their output byte by the
-  // multiplier (x 1 -> byte 2, x 256 -> byte 3) and merged with LOP3 bit-selects.
+  // (S + 4) / 9 for S <= 2295 is floor((S + 4) * 7282 / 65536) (exact: 9 * 7282 = 2^16 + 2 and 2299 * 2 < 2^16; the
+  // remainder term is at most 8 * 7282 + 2 * 255 = 58766).  The quotients are taken on the FMA pipe, straight from
+  // the packed u16x2 sums, with 64-bit multiply-adds (IMAD.HI with a 64-bit addend) - no lane extraction on the ALU
+  // pipe, which is the one that limits the fused kernels:
+  //   high lane: hi32(S2 * 7282 + K), S2 = lo + hi * 2^16.  The low lane's product adds (lo + 4) * 7282 >> 16 <= 255 to
+  //              the high lane's remainder: 58766 + 255 < 65536, the quotient is not disturbed;
+  //   low lane : hi32((S2 << 16) * 7282 + K'), the shift drops the high lane.
+  // Four clean byte values are then merged with multiply-adds by 2^8 / 2^16 (FMA pipe again).
+  // Written in C so that ptxas picks IMAD.HI.U32 (one instruction per quotient); the quotient then passes an empty
+  // asm so that the compiler cannot fuse ">> 32, * 256" into 64-bit funnel shifts + masks on the ALU pipe, and the
+  // merges are explicit mad.lo (IMAD).
+  static __device__ __forceinline__ uint32_t opaque(uint32_t v) {
+    asm("" : "+r"(v));
+    return v;
+  }
+  static __device__ __forceinline__ uint32_t mad_lo(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+  }
+  static __device__ __forceinline__ uint32_t q_hi(uint32_t s2) {
+    return opaque((uint32_t)(((uint64_t)s2 * 7282u + (uint64_t)(4u * 7282u) * 0x10001ull) >> 32));
+  }
+  static __device__ __forceinline__ uint32_t q_lo(uint32_t s2) {
+    return opaque((uint32_t)(((uint64_t)mad_lo(s2, 65536u, 0u) * 7282u + ((uint64_t)(4u * 7282u) << 16)) >> 32));
+  }
   static __device__ __forceinline__ void vcomb(const Part& t, const Part& m, const Part& b, uint32_t (&out)[KW]) {
 #pragma unroll
     for (int i = 0; i < KW; ++i) {
       const uint32_t se = t.e[i] + m.e[i] + b.e[i], so = t.o[i] + m.o[i] + b.o[i];
-      const uint32_t q0 = (se & 0xffffu) * 7282u + 4u * 7282u;                    // byte 2 = out byte 0
-      const uint32_t q1 = (so & 0xffffu) * (7282u * 256u) + 4u * 7282u * 256u;    // byte 3 = out byte 1
-      const uint32_t q2 = (se >> 16) * 7282u + 4u * 7282u;                        // byte 2 = out byte 2
-      const uint32_t q3 = (so >> 16) * (7282u * 256u) + 4u * 7282u * 256u;        // byte 3 = out byte 3
-      const uint32_t lo = bitsel<0x00ffffffu>(q0, q1);
-      const uint32_t hi = bitsel<0x00ffffffu>(q2, q3);
-      out[i] = prmt_c(lo, hi, 0x7632);
+      const uint32_t lo = mad_lo(q_lo(so), 256u, q_lo(se));          // out bytes 1, 0
+      const uint32_t hi = mad_lo(q_hi(so), 256u, q_hi(se));          // out bytes 3, 2
+      out[i] = mad_lo(hi, 65536u, lo);
     }
   }
 };

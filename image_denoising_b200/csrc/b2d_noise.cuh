@@ -42,7 +42,7 @@ struct GroupCtx {
 
 __device__ __forceinline__ uint4 group_random(const NoiseArgs& a, const GroupCtx& g, uint32_t sub) {
   const uint64_t gi = a.first_global + g.img_local;
-  return philox4x32_10(g.group, sub, (uint32_t)gi, (uint32_t)(gi >> 32), a.k0, a.k1);
+  return philox4x32(g.group, sub, (uint32_t)gi, (uint32_t)(gi >> 32), a.k0, a.k1);
 }
 __device__ __forceinline__ uint32_t r16(const uint4& r, int i) {
   const uint32_t w = (i >> 1) == 0 ? r.x : (i >> 1) == 1 ? r.y : (i >> 1) == 2 ? r.z : r.w;

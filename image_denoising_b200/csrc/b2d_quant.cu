@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(256) k_quant_fit(ImageSet s, int k, uint32_t k
   const uint64_t gi = first_global + (uint64_t)img_local;
   const uint32_t npix = (uint32_t)(s.h * s.w);
   for (int i = tid; i < Q_SAMPLES / 4; i += 256) {
-    const uint4 r = philox4x32_10((uint32_t)i, 0xC0u, (uint32_t)gi, (uint32_t)(gi >> 32), k0, k1);
+    const uint4 r = philox4x32((uint32_t)i, 0xC0u, (uint32_t)gi, (uint32_t)(gi >> 32), k0, k1);
     const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(256) k_quant_fit(ImageSet s, int k, uint32_t k
     return d0 * d0 + d1 * d1 + d2 * d2;
   };
   // ---- k-means++ seeding: next centre drawn with probability proportional to min distance^2
-  const uint4 ru = philox4x32_10(0u, 0xC1u, (uint32_t)gi, (uint32_t)(gi >> 32), k0, k1);
+  const uint4 ru = philox4x32(0u, 0xC1u, (uint32_t)gi, (uint32_t)(gi >> 32), k0, k1);
   if (tid == 0) {
     const uint32_t v = smp[ru.x % Q_SAMPLES];
     cen[0][0] = (float)(v & 255u); cen[0][1] = (float)((v >> 8) & 255u); cen[0][2] = (float)((v >> 16) & 255u);
@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(256) k_quant_fit(ImageSet s, int k, uint32_t k
     if (tid == 0) {
       float tot = 0.f;
       for (int t = 0; t < 256; ++t) tot += part[t];
-      const uint4 rc = philox4x32_10((uint32_t)c, 0xC2u, (uint32_t)gi, (uint32_t)(gi >> 32), k0, k1);
+      const uint4 rc = philox4x32((uint32_t)c, 0xC2u, (uint32_t)gi, (uint32_t)(gi >> 32), k0, k1);
       float target = tot * ((float)(rc.x >> 8) * (1.0f / 16777216.0f));
       int t = 0;
       while (t < 255 && target >= part[t]) { target -= part[t]; ++t; }

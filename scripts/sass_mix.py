@@ -28,12 +28,19 @@ def opcode(ins):
     return ins.split()[0]
 
 
+def klass(op):
+    parts = op.split(".")
+    if parts[0] in ("IMAD", "MUFU", "LDS", "STS", "LDG", "STG") and len(parts) > 1:
+        return parts[0] + "." + parts[1]
+    return parts[0]
+
+
 def main():
     path, pat = sys.argv[1], sys.argv[2]
     for name, ins in functions(path).items():
         if pat not in name:
             continue
-        ops = collections.Counter(opcode(i).split(".")[0] + ("." + opcode(i).split(".")[1] if opcode(i).startswith(("IMAD", "MUFU", "LDS", "STS", "LDG", "STG")) and "." in opcode(i) else "") for i in ins)
+        ops = collections.Counter(klass(opcode(i)) for i in ins)
         print(name, len(ins), "instructions")
         for k, v in ops.most_common():
             print("  %-14s %5d" % (k, v))

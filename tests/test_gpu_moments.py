@@ -106,3 +106,49 @@ def test_brownian_increments(cuda):
         d = (d + 128) % 256 - 128                       # unwrap single-step differences
         assert f[0] == 0
         assert abs(d.std() / (np.sqrt(0.009) * 255) - 1) < 0.03
+
+
+def _corr(a, b):
+    a = a - a.mean()
+    b = b - b.mean()
+    return float((a * b).mean() / np.sqrt((a * a).mean() * (b * b).mean()))
+
+
+def test_generator_independence(cuda):
+    """What the round count of the counter-based generator (Philox4x32-7, csrc/b2d_common.cuh) must deliver here:
+    draws that are uncorrelated along the element index (lags 1..16 cross the 8-element group = one Philox block,
+    lag 3 W = the pixel below), between consecutive images (counter words c2 / c3), between consecutive seeds
+    (key), and between the two fields of one draw; every one of the 16 bits of a draw balanced and the bits
+    pairwise independent; the 16-bit draws uniform (chi-square over 4096 cells)."""
+    from image_denoising_b200 import api
+    plan = api.get_plan(N, H, W, "uniform_var1.2", 0)
+    n_img = H * W * 3
+    x = plan.noise_field(seed=3)[0].double().cpu().numpy().ravel()
+    k = np.floor(x / 1.2 * 65536.0).astype(np.int64)            # the 16-bit draws: x = high * (k + 0.5) / 65536
+    assert k.min() >= 0 and k.max() <= 65535
+    lim = 5.0 / np.sqrt(x.size)
+    for lag in list(range(1, 17)) + [3 * W, 3 * W + 1, 3 * W - 1, n_img]:      # n_img: same element, next image
+        assert abs(_corr(x[:-lag], x[lag:])) < lim, lag
+    y = plan.noise_field(seed=4)[0].double().cpu().numpy().ravel()              # next seed
+    assert abs(_corr(x, y)) < lim
+    z = plan.noise_field(seed=3, first_index=1)[0].double().cpu().numpy().ravel()   # shifted image indices: same stream, moved
+    assert np.array_equal(z[: 3 * n_img], x[n_img:])
+    bits = ((k[:, None] >> np.arange(16)[None, :]) & 1).astype(np.float64)
+    assert np.abs(bits.mean(0) - 0.5).max() < 5 * 0.5 / np.sqrt(k.size)
+    cc = np.corrcoef(bits.T)
+    assert np.abs(cc - np.eye(16)).max() < lim
+    cells = np.bincount(k >> 4, minlength=4096).astype(np.float64)
+    chi2 = ((cells - k.size / 4096.0) ** 2 / (k.size / 4096.0)).sum()
+    assert abs(chi2 - 4095) < 6 * np.sqrt(2 * 4095), chi2                        # chi-square(4095): mean 4095, sd 90.5
+    # Gaussian field: both members of a Box-Muller pair, neighbouring pairs, squares (no variance clustering)
+    g = api.get_plan(N, H, W, "gaussian_var1.0", 0).noise_field(seed=3)[0].double().cpu().numpy().ravel()
+    for lag in (1, 2, 3, 7, 8, 9, 3 * W, n_img):
+        assert abs(_corr(g[:-lag], g[lag:])) < lim, lag
+        assert abs(_corr(g[:-lag] ** 2, g[lag:] ** 2)) < lim, lag
+    # s&p: the flip draw and the salt bit of one element, and of neighbours
+    u1, u2 = api.get_plan(N, H, W, "sap_var0.4", 0).noise_field(seed=3)
+    u1, u2 = u1.double().cpu().numpy().ravel(), u2.double().cpu().numpy().ravel()
+    f, s = (u1 < 0.4).astype(np.float64), (u2 < 0.5).astype(np.float64)
+    assert abs(_corr(f, s)) < lim
+    for lag in (1, 2, 7, 8, 3 * W):
+        assert abs(_corr(f[:-lag], f[lag:])) < lim and abs(_corr(s[:-lag], s[lag:])) < lim and abs(_corr(f[:-lag], s[lag:])) < lim, lag
