@@ -44,7 +44,7 @@ class B2DError(RuntimeError):
 
 EXPORTS = ["b2d_parse_spec", "b2d_plan_create", "b2d_plan_workspace_bytes", "b2d_plan_destroy", "b2d_run",
            "b2d_run_host", "b2d_host_register", "b2d_host_unregister", "b2d_noise_field", "b2d_wavelet_stats", "b2d_stats", "b2d_lab_convert",
-           "b2d_poisson_table", "b2d_gamma_table", "b2d_blob_shape", "b2d_blob_prep", "b2d_jpeg_info", "b2d_jpeg_create", "b2d_jpeg_decode", "b2d_jpeg_destroy", "b2d_jpeg_entropy", "b2d_nms", "b2d_nms_workspace_bytes", "b2d_nms_device",
+           "b2d_poisson_table", "b2d_gamma_table", "b2d_blob_shape", "b2d_blob_prep", "b2d_jpeg_info", "b2d_jpeg_create", "b2d_jpeg_decode", "b2d_jpeg_destroy", "b2d_jpeg_entropy", "b2d_nms", "b2d_nms_workspace_bytes", "b2d_nms_device", "b2d_nms_device_static",
            "b2d_launch_count", "b2d_reset_launch_count", "b2d_last_error", "b2d_version"]
 
 _lib = None
@@ -102,7 +102,8 @@ def lib():
     L.b2d_nms.argtypes = [vp, ip, vp, ctypes.c_int, ctypes.c_int, ctypes.c_float, ctypes.c_int]
     L.b2d_nms_workspace_bytes.argtypes = [ctypes.c_int, ctypes.POINTER(sz)]
     L.b2d_nms_device.argtypes = [vp, ctypes.c_int, ctypes.c_int, ctypes.c_float, vp, vp, vp, vp]
-    for name in ("b2d_nms", "b2d_nms_workspace_bytes", "b2d_nms_device"):
+    L.b2d_nms_device_static.argtypes = [vp, ctypes.c_int, ctypes.c_int, ctypes.c_float, vp, vp, vp]
+    for name in ("b2d_nms", "b2d_nms_workspace_bytes", "b2d_nms_device", "b2d_nms_device_static"):
         getattr(L, name).restype = ctypes.c_int
     L.b2d_launch_count.restype = u64
     L.b2d_reset_launch_count.restype = None

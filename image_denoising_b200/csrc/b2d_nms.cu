@@ -18,6 +18,8 @@
 #include "b2d_kernels.cuh"
 #include "b2d_plan.h"
 
+#include <mutex>
+
 namespace b2d {
 
 __device__ __forceinline__ float nms_iou(const float4 a, const float4 b) {
@@ -182,3 +184,62 @@ int b2d_nms(int* keep_out, int* num_out, const float* boxes_host, int boxes_num,
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------
+// b2d_nms_device_static: b2d_nms_device for callers that may not allocate (CUDA graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The suppression mask - the only scratch the two kernels need - lives in a file-scope device array
+// sized for B2D_NMS_STATIC_MAX_BOXES boxes (4096 x 64 words = 2 MiB), held by every GPU that loads the library
+// until the process exits.
+//
+// `g_nms_static_mask` is a HOST-side stand-in in host code, not a device address: the address a kernel can use
+// comes from cudaGetSymbolAddress, asked once per device with that device current (nms_static_mask below).
+//
+// Contents: k_nms_mask writes every word k_nms_sweep reads (the upper-triangular tiles of rows < n, in the row
+// pitch cb of THIS call), so nothing has to start at zero and the previous call's bits - left in place, also
+// under another pitch - are never read.  The array is shared by every call on a device: calls that overlap on
+// the GPU (different streams, no ordering between them) race on it.
+// ---------------------------------------------------------------------------------------------------------
+namespace b2d {
+
+constexpr int kNmsStaticMaxBoxes = B2D_NMS_STATIC_MAX_BOXES;
+constexpr size_t kNmsStaticWords = (size_t)kNmsStaticMaxBoxes * ((kNmsStaticMaxBoxes + 63) / 64);
+
+static __device__ __align__(256) unsigned long long g_nms_static_mask[kNmsStaticWords];
+
+// device address of the array on the CURRENT device; set up once per device, under a lock
+static int nms_static_mask(unsigned long long** out) {
+  static unsigned long long* addr[64] = {};
+  static std::mutex mu;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail_cuda(e, "cudaGetDevice");
+  if (dev < 0 || dev >= 64) return fail(B2D_ERR_UNSUPPORTED, "b2d_nms_device_static: device index %d beyond 63", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_nms_static_mask);
+    if (e != cudaSuccess) return fail_cuda(e, "cudaGetSymbolAddress(g_nms_static_mask)");
+    if (!p) return fail(B2D_ERR_CUDA, "cudaGetSymbolAddress(g_nms_static_mask) returned a null address");
+    addr[dev] = static_cast<unsigned long long*>(p);
+  }
+  *out = addr[dev];
+  return B2D_OK;
+}
+
+}  // namespace b2d
+
+extern "C" int b2d_nms_device_static(const float* d_boxes, int boxes_num, int boxes_dim, float nms_overlap_thresh,
+                                     int* d_keep, int* d_num, void* cuda_stream) {
+  if (!d_num || boxes_num < 0 || boxes_dim < 4) return fail(B2D_ERR_INVALID, "b2d_nms_device_static: bad argument");
+  if (boxes_num > kNmsStaticMaxBoxes)
+    return fail(B2D_ERR_INVALID, "b2d_nms_device_static: %d boxes exceed the static scratch (B2D_NMS_STATIC_MAX_BOXES = %d); "
+                                 "use b2d_nms_device with a caller-owned workspace", boxes_num, kNmsStaticMaxBoxes);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
+  if (boxes_num == 0) { CKN(cudaMemsetAsync(d_num, 0, sizeof(int), st)); return B2D_OK; }
+  if (!d_boxes || !d_keep) return fail(B2D_ERR_INVALID, "b2d_nms_device_static: null buffer");
+  unsigned long long* mask = nullptr;
+  const int rc = nms_static_mask(&mask);
+  if (rc != B2D_OK) return rc;
+  return nms_launch(d_boxes, boxes_num, boxes_dim, nms_overlap_thresh, d_keep, d_num, mask, st);
+}

@@ -249,6 +249,20 @@ int b2d_nms_workspace_bytes(int boxes_num, size_t* bytes);
 int b2d_nms_device(const float* d_boxes, int boxes_num, int boxes_dim, float nms_overlap_thresh, int* d_keep, int* d_num,
                    void* d_ws, void* cuda_stream);
 
+/* b2d_nms_device without any allocation and without a caller workspace.  NO COUNTERPART IN THE REFERENCE: added
+ *   for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ *   serving loops, harnesses that forbid it).  Same arguments and result as b2d_nms_device minus d_ws: the suppression
+ *   mask lives in a static device array inside the library, 2 MiB (B2D_NMS_STATIC_MAX_BOXES boxes x 64 words), held
+ *   by every GPU that loads the library until the process exits.  Runs on the CURRENT device, asynchronous on
+ *   cuda_stream; calls neither cudaMalloc / cudaFree nor any allocating library routine (its first call on a device
+ *   resolves the array's address with cudaGetSymbolAddress - make that call before starting a capture).
+ *   boxes_num > B2D_NMS_STATIC_MAX_BOXES fails with B2D_ERR_INVALID and a message naming the limit.
+ *   Every call on a device shares the array and leaves its bits there; each call rewrites all the words it reads, so
+ *   results never depend on earlier calls - but calls that OVERLAP on the GPU (two streams, no ordering) race. */
+#define B2D_NMS_STATIC_MAX_BOXES 4096
+int b2d_nms_device_static(const float* d_boxes, int boxes_num, int boxes_dim, float nms_overlap_thresh, int* d_keep,
+                          int* d_num, void* cuda_stream);
+
 /* Per-image result statistics gathered after the run (8(e): the only data
  * that ever crosses GPUs): checksum = sum of bytes * (1 + index mod 251)
  * mod 2^64 of d_out[i]; sse = sum (d_out - d_ref)^2 (for PSNR vs clean). */
