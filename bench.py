@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py - headline benchmark of the corrupt -> denoise hot path.
 
-Metric (BASELINE.json): Mpixels/s per noise x denoise.  Workload at every N:
+Metric (BASELINE.json): Mpixels/s per noise x denoise.  Headline workload at every N:
 BASELINE config C2 per GPU - a 512 x 600 x 1000 x 3 uint8 batch resident in
 HBM, one "step" = the two bandwidth-bound combinations named there
 (`sap_mean_var0.4` and `gaussian_gaus_blur_var1.5`) applied to the whole batch.
@@ -10,8 +10,16 @@ rank * 512 + i), no collective on the data path.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
 
-One JSON line on stdout (rank 0).  `--impl reference` times the CPU oracle
-(the transcription of the reference's closures over cv2 / NumPy) on the host.
+One JSON line on stdout (rank 0).  Beside the contract keys it carries
+  roofline    HBM fraction (the contract's bound / achieved / peak / frac) AND the instruction-issue fraction of
+              the dominant kernel, with `binding` naming the resource that actually limits it;
+  configs     all five BASELINE configs at full size (C1, C3, C4, C5 beside the headline C2), device timed, each with
+              its SURVEY 8(d) roofline and a CPU baseline of the same closures on the host cores;
+  strong      under --gpus N: C3 and C5 with the batch cut in N (shard.partition), max-over-ranks time, against the
+              same batch on one GPU measured in the same run;
+  psnr        mean PSNR of each headline spec against the clean batch, per-image (checksum, sse) gathered over NCCL;
+  e2e         b2d_run_host with pinned host buffers, plus the box's plain-copy ceiling measured in the same run.
+`--impl reference` times the CPU oracle (the transcription of the reference's closures over cv2 / NumPy) on the host.
 """
 import argparse
 import json
@@ -30,10 +38,37 @@ SPECS = ["sap_mean_var0.4", "gaussian_gaus_blur_var1.5"]
 N_IMAGES, H, W = 512, 600, 1000
 SEED = 3                                   # cfg.RNG_SEED (lib/model/config.py:255)
 ALGO_BYTES_PER_PIXEL = 6.0                 # 3 B read + 3 B written
-# dram__bytes_read.sum + dram__bytes_write.sum per launch of the two fused kernels at this workload,
-# from the `ncu --set full` capture profiles/r01h_fused3_full_raw.csv (same figures as r01c) (algorithmic: 1843.2 MB)
-NCU_TRAFFIC_BYTES = {"sap_mean_var0.4": 921654016 + 875183104, "gaussian_gaus_blur_var1.5": 921668352 + 874184704}
 WORKLOAD = "C2: 512x600x1000 RGB uint8 per GPU; step = sap_mean_var0.4 + gaussian_gaus_blur_var1.5"
+METRIC = "Mpixels/s per noise x denoise (mean over the step's combos)"
+SUBPARTITIONS = 148 * 4                    # warp schedulers of one B200: 1 warp instruction per cycle each
+LANE_INSTR_PEAK_T = 37.2                   # 148 SMs x 128 lanes x 1.965 GHz
+
+
+def shared_config():
+    """The `config` object: identical in the b200 and the reference arm (the driver compares them)."""
+    return {"workload": WORKLOAD, "specs": SPECS, "seed": SEED,
+            "l2": "inputs 921.6 MB per GPU > 126 MB L2, no flush needed"}
+
+
+def c5_specs(n, seed=SEED):
+    """C5: per image one of poisson / periodic / brownian / quant at a drawn level -> median 7x7."""
+    levels = {"periodic": ["3.14", "100", "size"], "brownian": ["0.9", "0.09", "0.009"], "quant": ["3", "7", "10"]}
+    out = []
+    for i in range(n):
+        hsh = (i * 2654435761 + seed * 40503) & 0xffffffff
+        noise = ["poisson", "periodic", "brownian", "quant"][(hsh >> 8) % 4]
+        out.append(noise + "_median" + ("" if noise == "poisson" else "_var" + levels[noise][(hsh >> 16) % 3]))
+    return out
+
+
+# name, images, H, W, specs (None = the C5 draw), spec overrides (device), oracle keyword arguments, roofline kind
+CONFIGS = [
+    ("C1", 16, 600, 1000, ["gaussian_median_var1.0"], {}, {}, "latency"),
+    ("C3", 1024, 1080, 1920, ["speckle_bilateral_var1.0"], {}, {}, "instr:539"),
+    ("C4", 256, 2048, 2048, ["gaussian_wavelet_var1.5"], {"wavelet": "db1", "levels": 3}, {"wavelet": "db1", "wavelet_levels": 3}, "hbm:9"),
+    ("C5", 4096, 600, 1000, None, {"ksize": 7}, {"median_k": 7}, "instr"),
+]
+STRONG = ("C3", "C5")
 
 
 def smooth_batch_torch(n, h, w, device, seed):
@@ -45,7 +80,7 @@ def smooth_batch_torch(n, h, w, device, seed):
     x = torch.arange(w, device=device, dtype=torch.float32).view(1, 1, w, 1)
     c = torch.arange(3, device=device, dtype=torch.float32).view(1, 1, 1, 3)
     out = torch.empty((n, h, w, 3), dtype=torch.uint8, device=device)
-    step = 64
+    step = max(1, min(64, (1 << 28) // (h * w * 3)))
     for i in range(0, n, step):
         m = min(step, n - i)
         ph = torch.rand((m, 1, 1, 1), generator=g, device=device) * 6.28
@@ -92,45 +127,105 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
+# --------------------------------------------------------------------------------------------------------
+# CPU legs: the oracle (kind "port": the reference's closures transcribed over the same cv2 / NumPy / SciPy /
+# sklearn calls) on the box's host cores.  The only place bench.py touches oracle/.
+# --------------------------------------------------------------------------------------------------------
 def _cpu_worker(args):
     import cv2
     cv2.setNumThreads(1)
     from oracle import closures as C
-    spec, imgs, seed = args
+    specs, imgs, seed, kw = args
     rng = np.random.RandomState(seed)
-    return [C.corrupt(im, spec, rng=rng).shape[0] for im in imgs]
+    return [C.corrupt(im, sp, rng=rng, **kw).shape[0] for im, sp in zip(imgs, specs)]
 
 
-def cpu_reference(images, specs, workers, repeats=1, min_seconds=0.0):
-    """The oracle (kind 'port': the reference's closures transcribed over the
-    same cv2 / NumPy calls) on `workers` host processes; returns Mpix/s."""
+def cpu_reference(jobs, workers, repeats=1, min_seconds=0.0):
+    """jobs: list of (spec, image, oracle kwargs), one closure call each, spread over `workers` forked processes
+    (cv2 threads = 1 each).  Returns (best pass seconds, passes)."""
     import multiprocessing as mp
-    n = len(images)
-    chunks = [images[i::workers] for i in range(workers) if len(images[i::workers])]
-    jobs = [(s, ch, SEED + k) for s in specs for k, ch in enumerate(chunks)]
-    best = None
+    per = [jobs[i::workers] for i in range(workers) if jobs[i::workers]]
+    packed = [([j[0] for j in ch], [j[1] for j in ch], SEED + k, ch[0][2]) for k, ch in enumerate(per)]
+    best, passes = None, 0
     with mp.get_context("fork").Pool(workers) as pool:
-        pool.map(_cpu_worker, [(specs[0], images[:1], 0)] * workers)       # warm the pool
-        passes = 0
+        pool.map(_cpu_worker, [([jobs[0][0]], [jobs[0][1]], 0, jobs[0][2])] * workers)       # warm the pool
         t_all = time.perf_counter()
         while True:
             t0 = time.perf_counter()
-            pool.map(_cpu_worker, jobs, chunksize=1)
+            pool.map(_cpu_worker, packed, chunksize=1)
             dt = time.perf_counter() - t0
             best = dt if best is None else min(best, dt)
             passes += 1
             if passes >= repeats and time.perf_counter() - t_all >= min_seconds:
                 break
-    mpix = n * len(specs) * images[0].shape[0] * images[0].shape[1] / 1e6
-    cpu_reference.passes = passes
-    return mpix / best, best
+    return best, passes
 
 
-def host_sample(n, seed):
+def host_sample(n, h, w, seed):
     """CPU-side sample of the same synthetic workload (SURVEY.md 8(d) `smooth`)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from conftest import synth_image
-    return [synth_image(H, W, seed + i, "smooth") for i in range(n)]
+    return [synth_image(h, w, seed + i, "smooth") for i in range(n)]
+
+
+def cpu_baseline_c2(workers, n_s, min_seconds):
+    imgs = host_sample(n_s, H, W, 1002)
+    t_cpu = time.perf_counter()
+    dt, passes = cpu_reference([(s, im, {}) for s in SPECS for im in imgs], workers, min_seconds=min_seconds)
+    v = n_s * len(SPECS) * H * W / 1e6 / dt
+    return {"value": v, "unit": "Mpix/s", "cores": workers, "kind": "port",
+            "sample": "%d of %d images per spec, %d passes (best pass %.2f s, %.0f s of CPU work in total), "
+                      "%d processes, cv2 threads=1 each" % (n_s, N_IMAGES, passes, dt, time.perf_counter() - t_cpu, workers)}
+
+
+def cpu_baseline_config(name, n, h, w, specs, okw, workers):
+    """One pass of `workers` images (one per process) of a BASELINE config through the oracle."""
+    n_s = min(n, workers)
+    imgs = host_sample(min(n_s, 4), h, w, 1000 + int(name[1]) * 100)
+    per_image = c5_specs(n)[:n_s] if specs is None else None
+    jobs = []
+    for i in range(n_s):
+        for s in ([per_image[i]] if per_image else specs):
+            jobs.append((s, imgs[i % len(imgs)], okw))
+    dt, passes = cpu_reference(jobs, workers)
+    passes_per_image = 1 if per_image else len(specs)
+    return {"value": n_s * passes_per_image * h * w / 1e6 / dt, "unit": "Mpix/s", "cores": workers, "kind": "port",
+            "sample": "%d of %d images, 1 pass of %.2f s, %d processes, cv2 threads=1 each" % (n_s, n, dt, workers)}
+
+
+def cpu_legs():
+    """`bench.py --cpu-legs` (a FRESH process, started by the b200 arm with OMP / BLAS threads = 1): the CPU baselines
+    of all five configs as one JSON object on stdout.  Not forked from the CUDA process: torch's OpenMP pool does not
+    survive a fork, and the C5 quant branch (sklearn) would hang in the child."""
+    workers = os.cpu_count() or 1
+    out = {"C2": cpu_baseline_c2(workers, max(2 * workers, 32), 10.0)}
+    for cfg in CONFIGS:
+        t0 = time.perf_counter()
+        out[cfg[0]] = cpu_baseline_config(cfg[0], cfg[1], cfg[2], cfg[3], cfg[4], cfg[6], workers)
+        log("cpu leg %s: %.1f s" % (cfg[0], time.perf_counter() - t0))
+    print(json.dumps(out))
+    return 0
+
+
+def run_cpu_legs_subprocess(limit_s=300):
+    env = dict(os.environ, OMP_NUM_THREADS="1", OPENBLAS_NUM_THREADS="1", MKL_NUM_THREADS="1", CUDA_VISIBLE_DEVICES="")
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        env.pop(k, None)
+    try:
+        res = subprocess.run([sys.executable, os.path.abspath(__file__), "--cpu-legs"], env=env, stdout=subprocess.PIPE,
+                             stderr=sys.stderr, text=True, timeout=limit_s)
+        return json.loads(res.stdout.strip().splitlines()[-1])
+    except (subprocess.TimeoutExpired, ValueError, IndexError) as e:
+        log("cpu legs failed: %r" % (e,))
+        return {}
+
+
+_T0 = time.perf_counter()
+
+
+def log(msg):
+    """progress on stderr (stdout carries the one JSON line)"""
+    print("[bench %7.1f s] %s" % (time.perf_counter() - _T0, msg), file=sys.stderr, flush=True)
 
 
 def run_reference(args):
@@ -139,10 +234,11 @@ def run_reference(args):
         return 0
     workers = os.cpu_count() or 1
     per_step = max(workers, 16)                       # bounded sample: >= 16 images per spec per step
-    imgs = host_sample(per_step, 1002)
+    imgs = host_sample(per_step, H, W, 1002)
+    jobs = [(s, im, {}) for s in SPECS for im in imgs]
     times = []
     for i in range(args.warmup + args.steps):
-        v, dt = cpu_reference(imgs, SPECS, workers)
+        dt, _ = cpu_reference(jobs, workers)
         if i >= args.warmup:
             times.append(dt)
     mpix_step = per_step * len(SPECS) * H * W / 1e6
@@ -150,57 +246,181 @@ def run_reference(args):
     value = mpix_step / t
     sample = "%d images of %dx%d per spec per step (of %d), %d processes, cv2 threads=1 each" % (
         per_step, H, W, N_IMAGES, workers)
-    line = {"impl": "reference", "metric": "Mpixels/s per noise x denoise (mean over the step's combos)",
+    line = {"impl": "reference", "metric": METRIC,
             "value": value, "unit": "Mpix/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64 noise + u8 filters (NumPy/OpenCV)", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "specs": SPECS, "sample": sample},
+            "config": shared_config(),
             "cpu_baseline": {"value": value, "unit": "Mpix/s", "cores": workers, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
     return 0
 
 
-def run_b200(args):
-    import torch
-    import torch.distributed as dist
-    from image_denoising_b200 import _lib, api
+# --------------------------------------------------------------------------------------------------------
+# b200 arm
+# --------------------------------------------------------------------------------------------------------
+class Ctx:
+    """torch / distributed handles of one rank."""
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device (there is no CPU fallback for --impl b200)")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+    def __init__(self):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device (there is no CPU fallback for --impl b200)")
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, x):
+        t = self.torch.tensor([x], device=self.dev, dtype=self.torch.float64)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return t.item()
+
+
+def time_plans(cx, plans, batch, out, first, steps, warmup=3):
+    """ms per pass over `plans` (CUDA events on the launching stream, barrier + synchronize on both sides, max over
+    ranks)."""
+    torch = cx.torch
+    for _ in range(warmup):
+        for p in plans:
+            p.run(batch, out, SEED, first)
+    cx.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        for p in plans:
+            p.run(batch, out, SEED, first)
+    e1.record()
+    cx.barrier()
+    return cx.max_over_ranks(e0.elapsed_time(e1) / steps)
+
+
+def config_roofline(kind, mpix, ms, per_gpu, peak_gbs, peak_src):
+    """SURVEY 8(d) roofline of one config; mpix = pixels x passes of the whole job, per_gpu = GPUs sharing it."""
+    if kind.startswith("hbm"):
+        bpp = float(kind.split(":")[1])
+        gbs = mpix * 1e6 * bpp / (ms * 1e-3) / 1e9 / per_gpu
+        return {"bound": "hbm", "bytes_per_pixel": bpp, "achieved": gbs, "peak": peak_gbs, "peak_source": peak_src,
+                "unit": "GB/s", "frac": gbs / peak_gbs}
+    if kind == "instr:539":
+        t = mpix * 1e6 * 539 / (ms * 1e-3) / 1e12 / per_gpu
+        return {"bound": "fp32/int issue", "lane_instr_per_pixel": 539, "achieved": t, "peak": LANE_INSTR_PEAK_T,
+                "unit": "T lane-instr/s", "frac": t / LANE_INSTR_PEAK_T,
+                "note": "539 = SURVEY 8(d)'s algorithmic count for d = 9 (49 taps x 11); the kernel executes 467 per pixel"}
+    if kind == "latency":
+        gbs = mpix * 1e6 * 6.0 / (ms * 1e-3) / 1e9 / per_gpu
+        return {"bound": "latency", "achieved": gbs, "peak": peak_gbs, "unit": "GB/s", "frac": gbs / peak_gbs,
+                "note": "16 images = 624 CTAs, barely one wave of 148 SMs x 4: a launch-latency measurement, not a throughput one"}
+    return {"bound": "int issue (selection networks)", "frac": None,
+            "note": "k_median_blocks<7>: ALU pipe 92.9 % (profiles/r01e_median7_blocks_full_raw.csv), 181 compare-exchanges "
+                    "per output byte; the four pre-passes are HBM / fp64-scan bound"}
+
+
+def run_config(cx, cfg, shard_it, steps, peak_gbs, peak_src):
+    """One BASELINE config at full size, device timed.  shard_it: cut the batch over the ranks (strong scaling);
+    otherwise every rank runs the whole batch (the one-GPU figure, max over ranks)."""
+    from image_denoising_b200 import api, shard
+    torch = cx.torch
+    name, n, h, w, specs, over, _okw, kind = cfg
+    lo, cnt = shard.partition(n, cx.world)[cx.rank] if shard_it else (0, n)
+    batch = smooth_batch_torch(cnt, h, w, cx.dev, 1000 + int(name[1]))
+    out = torch.empty_like(batch)
+    if specs is None:
+        plans = [api.Plan(cnt, h, w, c5_specs(n)[lo:lo + cnt], cx.local, **over)]
+    else:
+        plans = [api.Plan(cnt, h, w, s, cx.local, **over) for s in specs]
+    ms = time_plans(cx, plans, batch, out, lo, steps)
+    mpix = n * h * w * len(plans) / 1e6
+    gpus = cx.world if shard_it else 1
+    res = {"config": name, "images": n, "shape": [h, w], "specs": specs or "mixed poisson/periodic/brownian/quant -> median 7x7",
+           "overrides": over, "ms": ms, "mpix_s": mpix / (ms * 1e-3), "gpus_sharing_the_batch": gpus,
+           "roofline": config_roofline(kind, mpix, ms, gpus, peak_gbs, peak_src)}
+    del plans, batch, out
+    api._PLANS.clear()
+    torch.cuda.empty_cache()
+    return res
+
+
+def copy_ceiling(cx, nbytes, reps=3):
+    """The box's plain-copy ceiling for the e2e step: the same bytes, pinned host memory, H2D and D2H at the same
+    time on two streams, no kernels - on every rank at once, max over ranks.  Returns seconds per (in + out) pass."""
+    torch = cx.torch
+    h_a = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    h_b = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    d_a = torch.empty(nbytes, dtype=torch.uint8, device=cx.dev)
+    d_b = torch.empty(nbytes, dtype=torch.uint8, device=cx.dev)
+    s1, s2 = torch.cuda.Stream(cx.dev), torch.cuda.Stream(cx.dev)
+    best = None
+    for i in range(reps + 1):
+        cx.barrier()
+        t0 = time.perf_counter()
+        with torch.cuda.stream(s1):
+            d_a.copy_(h_a, non_blocking=True)
+        with torch.cuda.stream(s2):
+            h_b.copy_(d_b, non_blocking=True)
+        torch.cuda.synchronize()
+        dt = cx.max_over_ranks(time.perf_counter() - t0)
+        if i > 0:
+            best = dt if best is None else min(best, dt)
+    return best
+
+
+def gather_psnr(cx, plan, out, ref, elems):
+    """Per-image (checksum u64, sse f64) on the device, all-gathered over NCCL (16 B per image: the only payload that
+    ever crosses GPUs); returns (xor of all checksums, mean PSNR in dB vs the clean batch)."""
+    from image_denoising_b200 import shard
+    torch = cx.torch
+    cs, sse = plan.stats(out, ref)
+    if cx.world > 1:
+        cs_all = shard.gather_per_image(cs, cx.world * out.shape[0])
+        sse = shard.gather_per_image(sse, cx.world * out.shape[0])
+    else:
+        cs_all = cs
+    mse = (sse / elems).clamp_min(1e-12)
+    psnr = (10.0 * torch.log10(255.0 ** 2 / mse)).mean().item()
+    return int(np.bitwise_xor.reduce(cs_all.cpu().numpy())), psnr
+
+
+def run_b200(args):
+    from image_denoising_b200 import _lib, api
+    cx = Ctx()
+    torch, world, rank, local, dev = cx.torch, cx.world, cx.rank, cx.local, cx.dev
     L = _lib.lib()
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    peaks = json.load(open(peaks_path)) if os.path.exists(peaks_path) else {}
+    peak_gbs, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    ncu_path = os.path.join(ROOT, "profiles", "ncu_constants.json")
+    ncu = json.load(open(ncu_path)) if os.path.exists(ncu_path) else {"kernels": {}}
 
     batch = smooth_batch_torch(N_IMAGES, H, W, dev, 1002 + rank)
     out = torch.empty_like(batch)
     first = rank * N_IMAGES
     plans = [api.Plan(N_IMAGES, H, W, s, local) for s in SPECS]
-    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
-        os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
-    peak_gbs, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
+    log("rank %d: inputs ready" % rank)
+    # ---- headline: K timed steps of the C2 step, inputs resident in HBM ----------------------------------
     for _ in range(args.warmup):
         for p in plans:
             p.run(batch, out, SEED, first)
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(SPECS) + 1)] for _ in range(args.steps)]
     clocks = ClockSampler(local)
-    barrier()
+    cx.barrier()
     if rank == 0:
         clocks.start()
     L.b2d_reset_launch_count()
-    t0 = torch.cuda.Event(enable_timing=True)
-    t1 = torch.cuda.Event(enable_timing=True)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0.record()
     for k in range(args.steps):
         ev[k][0].record()
@@ -208,7 +428,7 @@ def run_b200(args):
             p.run(batch, out, SEED, first)
             ev[k][j + 1].record()
     t1.record()
-    barrier()
+    cx.barrier()
     launches = int(L.b2d_launch_count())
     # nvidia-smi samples every 100 ms and the timed region may last only tens of ms: keep the
     # sampler running over a soak of the SAME step (not timed) so the clock record is meaningful
@@ -221,101 +441,131 @@ def run_b200(args):
     clk = clocks.stop() if rank == 0 else None
     if clk is not None:
         clk["window"] = "timed region + 1.5 s soak of the same step"
-    ms_total = t0.elapsed_time(t1)
-    tt = torch.tensor([ms_total], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    ms_step = tt.item() / args.steps
+    ms_step = cx.max_over_ranks(t0.elapsed_time(t1)) / args.steps
     per_kernel = [float(np.mean([ev[k][j].elapsed_time(ev[k][j + 1]) for k in range(args.steps)]))
                   for j in range(len(SPECS))]
     mpix_batch = N_IMAGES * H * W / 1e6
     value = world * len(SPECS) * mpix_batch / (ms_step * 1e-3)
+    if args.profile:
+        if rank == 0:
+            print(json.dumps({"profile_run": True, "ms_per_step": ms_step, "per_spec_ms": dict(zip(SPECS, per_kernel)),
+                              "gpu_launches": launches}))
+        return 0
 
-    # ---- end to end through the host-buffer C ABI call (b2d_run_host), pinned memory ----
+    log("headline timed: %.3f ms / step" % ms_step)
+    # ---- PSNR vs clean + checksums: per-image (checksum, sse) gathered over NCCL ---------------------------
+    psnr, checksum = {}, 0
+    for s, p in zip(SPECS, plans):
+        p.run(batch, out, SEED, first)
+        cs_xor, db = gather_psnr(cx, p, out, batch, H * W * 3)
+        psnr[s] = db
+        checksum ^= cs_xor
+
+    log("psnr gathered")
+    # ---- end to end through the host-buffer C ABI call (b2d_run_host), pinned memory -----------------------
     h_in = torch.empty((N_IMAGES, H, W, 3), dtype=torch.uint8).pin_memory()
     h_out = torch.empty_like(h_in).pin_memory()
     h_in.copy_(batch.cpu())
-    e2e_steps = 0 if args.profile else max(1, min(args.steps, 3))
-    if args.profile:
-        print(json.dumps({"profile_run": True, "ms_per_step": ms_step, "per_spec_ms": dict(zip(SPECS, per_kernel)),
-                          "gpu_launches": launches}))
-        return 0
+    e2e_steps = max(1, min(args.steps, 3))
     for p in plans:
         p.run_host(h_in, h_out, SEED, first)                       # warm-up (allocates staging buffers)
-    barrier()
+    cx.barrier()
     w0 = time.perf_counter()
     for _ in range(e2e_steps):
         for p in plans:
             p.run_host(h_in, h_out, SEED, first)
     torch.cuda.synchronize()
-    e2e_s = (time.perf_counter() - w0) / e2e_steps
-    te = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_value = world * len(SPECS) * mpix_batch / te.item()
+    e2e_s = cx.max_over_ranks((time.perf_counter() - w0) / e2e_steps)
+    e2e_value = world * len(SPECS) * mpix_batch / e2e_s
     nbytes = batch.numel()
+    del h_in, h_out
+    ceil_s = copy_ceiling(cx, nbytes)                              # one spec's bytes in + out, all ranks at once
+    ceiling = world * mpix_batch / ceil_s
 
-    # ---- per-image checksums gathered over NCCL (the only cross-GPU payload, 8 B/image) ----
-    cs, _ = plans[-1].stats(out)
-    if world > 1:
-        allcs = [torch.empty_like(cs) for _ in range(world)]
-        dist.all_gather(allcs, cs)
-        cs = torch.cat(allcs)
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return 0
-
+    log("e2e %.0f Mpix/s, ceiling %.0f" % (e2e_value, ceiling))
+    # ---- the filters alone (HBM bound) ----------------------------------------------------------------------
     filt = {}
     for fs in ("original_gaus_blur", "original_mean", "original_median"):
-        fp = api.Plan(N_IMAGES, H, W, fs, local)
-        for _ in range(3):
-            fp.run(batch, out, SEED, first)
-        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize()
-        f0.record()
-        for _ in range(10):
-            fp.run(batch, out, SEED, first)
-        f1.record()
-        torch.cuda.synchronize()
-        fms = f0.elapsed_time(f1) / 10
+        fms = time_plans(cx, [api.Plan(N_IMAGES, H, W, fs, local)], batch, out, first, 10)
         filt[fs] = {"ms": round(fms, 4), "hbm_frac": round(mpix_batch * 1e6 * ALGO_BYTES_PER_PIXEL / (fms * 1e-3) / 1e9 / peak_gbs, 3)}
-        del fp
-    dom = int(np.argmax(per_kernel))
-    achieved = mpix_batch * 1e6 * ALGO_BYTES_PER_PIXEL / (per_kernel[dom] * 1e-3) / 1e9
+    del plans
+    api._PLANS.clear()
+
+    # ---- all five BASELINE configs at full size; strong scaling of C3 / C5 under --gpus N --------------------
+    del batch, out
+    torch.cuda.empty_cache()
+    configs = [{"config": "C2", "images": N_IMAGES, "shape": [H, W], "specs": SPECS, "overrides": {}, "ms": ms_step,
+                "mpix_s": value / world, "gpus_sharing_the_batch": 1,
+                "roofline": config_roofline("hbm:6", len(SPECS) * mpix_batch, ms_step, 1, peak_gbs, peak_src)}]
+    strong = {}
+    cfg_steps = max(2, min(args.steps, 5))
+    for cfg in CONFIGS:
+        log("config %s" % cfg[0])
+        one = run_config(cx, cfg, False, cfg_steps, peak_gbs, peak_src)     # the whole batch on ONE GPU (every rank does it)
+        configs.append(one)
+        if world > 1 and cfg[0] in STRONG:
+            cut = run_config(cx, cfg, True, cfg_steps, peak_gbs, peak_src)  # the batch cut in `world`
+            strong[cfg[0]] = {"n_gpus": world, "ms_one_gpu": one["ms"], "ms": cut["ms"], "mpix_s": cut["mpix_s"],
+                              "speedup": one["ms"] / cut["ms"], "efficiency": one["ms"] / cut["ms"] / world,
+                              "timing": "CUDA events, max over ranks, batch cut with shard.partition"}
+    configs.sort(key=lambda c: c["config"])
+    if rank != 0:
+        if world > 1:
+            cx.dist.destroy_process_group()
+        return 0
+
+    # ---- CPU baselines (rank 0, N = 1 only: bounded samples on the host cores) -------------------------------
     cpu = None
     if world == 1:
-        workers = os.cpu_count() or 1
-        n_s = max(2 * workers, 32)
-        t_cpu = time.perf_counter()
-        v, dt = cpu_reference(host_sample(n_s, 1002), SPECS, workers, min_seconds=10.0)
-        cpu = {"value": v, "unit": "Mpix/s", "cores": workers, "kind": "port",
-               "sample": "%d of %d images per spec, %d passes (best pass %.2f s, %.0f s of CPU work in total), "
-                         "%d processes, cv2 threads=1 each" % (n_s, N_IMAGES, cpu_reference.passes, dt,
-                                                              time.perf_counter() - t_cpu, workers)}
-    line = {"metric": "Mpixels/s per noise x denoise (mean over the step's combos)", "value": value, "unit": "Mpix/s",
+        log("cpu legs (fresh subprocess)")
+        legs = run_cpu_legs_subprocess()
+        cpu = legs.get("C2")
+        for c in configs:
+            c["cpu_baseline"] = legs.get(c["config"])
+
+    # ---- roofline of the dominant kernel: HBM fraction (contract) and instruction-issue fraction -------------
+    dom = int(np.argmax(per_kernel))
+    algo_bytes = mpix_batch * 1e6 * ALGO_BYTES_PER_PIXEL
+    achieved = algo_bytes / (per_kernel[dom] * 1e-3) / 1e9
+    sm_mhz = (clk or {}).get("sm_mhz") or peaks.get("sm_max_mhz") or 1965.0
+    per_spec = {}
+    for s, t in zip(SPECS, per_kernel):
+        k = ncu["kernels"].get(s, {})
+        wi = k.get("warp_instructions")
+        per_spec[s] = {"ms": t, "mpix_s": mpix_batch / (t * 1e-3), "frac_hbm": algo_bytes / (t * 1e-3) / 1e9 / peak_gbs,
+                       "frac_issue": wi / (SUBPARTITIONS * sm_mhz * 1e6) / (t * 1e-3) if wi else None,
+                       "warp_instructions": wi, "dram_bytes": k.get("dram_bytes"), "psnr_db_vs_clean": psnr[s]}
+    kd = per_spec[SPECS[dom]]
+    binding = "issue" if (kd["frac_issue"] or 0.0) > kd["frac_hbm"] else "hbm"
+    roofline = {"bound": "hbm", "kernel": "k_fused3<%s>" % SPECS[dom], "achieved": achieved, "peak": peak_gbs,
+                "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak_gbs,
+                "traffic": kd["dram_bytes"], "algorithmic_bytes": algo_bytes,
+                "binding": binding, "frac_hbm": kd["frac_hbm"], "frac_issue": kd["frac_issue"],
+                "issue": {"warp_instructions": kd["warp_instructions"], "schedulers": SUBPARTITIONS, "sm_mhz": sm_mhz,
+                          "formula": "warp_instructions / (schedulers x sm_mhz) / kernel time"},
+                "ncu_source": ncu.get("source"), "ncu_git_sha": ncu.get("git_sha"),
+                "note": "the fused noise -> 3x3 kernels are bound by the generator's instructions (Philox on the FMA / ALU "
+                        "pipes, Box-Muller on the XU pipe), not by HBM: DRAM traffic equals the algorithmic bytes; the "
+                        "filters alone (detail.filter_only) are HBM bound"}
+    line = {"metric": METRIC, "value": value, "unit": "Mpix/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8 (fp32 noise math)",
-            "data": "synthetic",
-            "config": {"workload": WORKLOAD, "specs": SPECS, "seed": SEED,
-                       "l2": "inputs 921.6 MB per GPU > 126 MB L2, no flush needed",
-                       "per_spec_ms": dict(zip(SPECS, per_kernel)),
-                       "per_spec_mpix_s": {s: mpix_batch / (t * 1e-3) for s, t in zip(SPECS, per_kernel)},
-                       "filter_only": filt,
-                       "bound_note": "fused kernels are generator bound (Philox FMA/ALU pipes, Box-Muller XU pipe), "
-                                     "the filters alone are HBM bound: DESIGN.md section 5",
-                       "checksum_xor": int(np.bitwise_xor.reduce(cs.cpu().numpy()))},
+            "data": "synthetic", "config": shared_config(),
             "clocks": clk, "gpu_launches": launches,
             "e2e": {"value": e2e_value, "unit": "Mpix/s", "h2d_bytes_per_step": len(SPECS) * nbytes,
-                    "d2h_bytes_per_step": len(SPECS) * nbytes, "api": "b2d_run_host (pinned host buffers)"},
-            "roofline": {"bound": "hbm", "kernel": "k_fused3<%s>" % SPECS[dom], "achieved": achieved,
-                         "peak": peak_gbs, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak_gbs,
-                         "traffic": NCU_TRAFFIC_BYTES.get(SPECS[dom]), "traffic_source": "profiles/r01h_fused3_full_raw.csv",
-                         "algorithmic_bytes": mpix_batch * 1e6 * ALGO_BYTES_PER_PIXEL},
-            "cpu_baseline": cpu}
+                    "d2h_bytes_per_step": len(SPECS) * nbytes, "api": "b2d_run_host (pinned host buffers)",
+                    "ceiling_mpix_s": ceiling, "frac_of_ceiling": e2e_value / ceiling,
+                    "ceiling": "plain pinned H2D + D2H of one spec's bytes at the same time on two streams, no kernels, "
+                               "every rank at once (max over ranks), measured in this run"},
+            "roofline": roofline, "cpu_baseline": cpu,
+            "detail": {"per_spec": per_spec, "filter_only": filt, "checksum_xor": checksum},
+            "psnr": {"unit": "dB vs the clean batch, mean over all images of all ranks",
+                     "gathered": "per-image (checksum u64, sse f64) all_gather over NCCL" if world > 1 else "one rank",
+                     **psnr},
+            "configs": configs, "strong": strong or None}
     print(json.dumps(line))
     if world > 1:
-        dist.destroy_process_group()
+        cx.dist.destroy_process_group()
     return 0
 
 
@@ -326,7 +576,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--profile", action="store_true", help="device-timed part only (for runs under ncu)")
+    ap.add_argument("--cpu-legs", action="store_true", help=argparse.SUPPRESS)
     args = ap.parse_args()
+    if args.cpu_legs:
+        return cpu_legs()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     return run_reference(args) if args.impl == "reference" else run_b200(args)
 
