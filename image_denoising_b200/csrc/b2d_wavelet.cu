@@ -916,7 +916,9 @@ int run_wavelet(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, int ki
   for (int i = 0; i < 3; ++i)
     for (int j = 0; j < 3; ++j) fa.inv[i][j] = (float)inv[i][j];
   auto blocks = [](size_t n) { return (unsigned)std::min<size_t>((n + 255) / 256, 148 * 8); };
-  if (haar_supported(p, sp, mode)) return run_haar(p, s, kind, na, g, wbase, wavelet_workspace_bytes(p), fa.inv, st);
+  // the register-resident path loads / stores 8-byte words at img + multiples of 24: both batch bases must be 8-byte aligned
+  const bool base8 = ((reinterpret_cast<uintptr_t>(s.in) | reinterpret_cast<uintptr_t>(s.out)) & 7u) == 0;
+  if (base8 && haar_supported(p, sp, mode)) return run_haar(p, s, kind, na, g, wbase, wavelet_workspace_bytes(p), fa.inv, st);
 
   for (int first = 0; first < s.count; first += chunk) {
     const int cnt = std::min(chunk, s.count - first);

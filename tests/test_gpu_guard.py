@@ -1,0 +1,70 @@
+"""GPU: out-of-bounds-write and race checks of our own.  compute-sanitizer is closed on this pool (it answers
+"closed on this pool and stays closed": runs under it have left GPUs needing a reset), so instead:
+  * every kernel family writes into an output that sits between two canary bands inside a larger allocation, at an
+    aligned and at an odd byte offset (the partial-word stores at row ends, the funnel-shifted re-aligning stores and the
+    last-column handling are exactly what could spill); the bands and the INPUT must be untouched afterwards;
+  * every run is repeated and must give the same bytes (a shared-memory or apron race shows up as nondeterminism);
+  * the workspace is poisoned with 0xFF between the two runs (a read of scratch that was never written shows up too).
+scripts/sanitize_cases.py + scripts/sanitize.sh hold the sweep for a pool where the sanitizer is open."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import synth_batch
+
+pytestmark = pytest.mark.gpu
+
+GUARD = 8192
+SHAPES = [(2, 37, 53), (2, 50, 100), (1, 61, 99), (1, 130, 1368), (3, 24, 333), (1, 304, 320)]
+SPECS = [("sap_mean_var0.4", {}), ("gaussian_gaus_blur_var1.5", {}), ("speckle_median_var1.0", {}), ("shader", {}),
+         ("periodic_mean_var100", {}), ("gamma_gaus_blur_var0.1", {}), ("original_gaus_blur", {}), ("original_mean", {}),
+         ("original_median", {}), ("gaussian_var1.0", {}), ("poisson_median", {}), ("brownian_mean_var0.09", {}),
+         ("original_median", {"ksize": 5}), ("gaussian_median_var1.0", {"ksize": 7}), ("speckle_bilateral_var1.0", {}),
+         ("gaussian_wavelet_var1.5", {}), ("gaussian_wavelet_var1.5", {"wavelet": "db1", "levels": 3}),
+         ("quant_median_var7", {}), ("quant_wavelet_var3", {}), ("bloom", {})]
+
+
+@pytest.mark.parametrize("shape", SHAPES, ids=lambda s: "%dx%dx%d" % s)
+@pytest.mark.parametrize("offset", [0, 3])
+def test_no_write_outside_the_output_and_runs_repeat(cuda, shape, offset):
+    from image_denoising_b200 import api
+    n, h, w = shape
+    nbytes = n * h * w * 3
+    src = torch.from_numpy(synth_batch(n, h, w, seed=h * w, kind="smooth")).to(cuda)
+    arena_in = torch.full((nbytes + 2 * GUARD + 8,), 0x5A, dtype=torch.uint8, device=cuda)
+    arena_out = torch.full((nbytes + 2 * GUARD + 8,), 0xA5, dtype=torch.uint8, device=cuda)
+    lo = GUARD + offset
+    x = arena_in[lo:lo + nbytes].view(n, h, w, 3)
+    x.copy_(src)
+    y = arena_out[lo:lo + nbytes].view(n, h, w, 3)
+    bad = []
+    for spec, kw in SPECS:
+        if spec == "bloom" and h < 300:
+            continue
+        plan = api.get_plan(n, h, w, spec, cuda.index, **kw)
+        arena_out.fill_(0xA5)
+        plan.run(x, y, seed=5, first_index=2)
+        first = y.clone()
+        if not (bool((arena_out[:lo] == 0xA5).all()) and bool((arena_out[lo + nbytes:] == 0xA5).all())):
+            bad.append((spec, kw, "wrote outside the output"))
+        if not (torch.equal(x, src) and bool((arena_in[:lo] == 0x5A).all()) and bool((arena_in[lo + nbytes:] == 0x5A).all())):
+            bad.append((spec, kw, "touched the input"))
+            x.copy_(src)
+        ws = plan._workspace()
+        if ws is not None:
+            ws.fill_(0xFF)                                     # scratch read before written would now change the result
+        y.fill_(0)
+        plan.run(x, y, seed=5, first_index=2)
+        if not torch.equal(y, first):
+            bad.append((spec, kw, "second run differs", int((y != first).sum())))
+        if offset:                                             # an odd base address must not change the bytes either
+            aligned = plan.run(src, seed=5, first_index=2)
+            if kw.get("wavelet") == "db1" and h % 8 == 0 and w % 8 == 0:
+                # the register-resident Haar path needs 8-byte aligned bases; an odd base runs the general path, which
+                # agrees with it to <= 1 LSB on < 0.2 % of the pixels (tests/test_gpu_wavelet.py)
+                d = (aligned.int() - first.int()).abs()
+                if int(d.max()) > 1 or float((d > 0).float().mean()) > 2e-3:
+                    bad.append((spec, kw, "general vs Haar path", int(d.max()), float((d > 0).float().mean())))
+            elif not torch.equal(aligned, first):
+                bad.append((spec, kw, "unaligned base differs from aligned", int((aligned != first).sum())))
+    assert not bad, bad
