@@ -16,8 +16,8 @@
 // Work split: a lane owns 8 pixels x 2 rows (two 24-byte units = 6 Philox groups); 4 lanes
 // (lane & 3 = row pair) form one 8 x 8 block, a warp 8 blocks side by side (192 contiguous bytes
 // per row).  Along x all three levels are thread-local; along y level 1 is local, level 2 / 3
-// exchange partners with __shfl_xor(1) / (2).  Arithmetic mirrors the general kernels operation
-// for operation (analysis: separate multiplies and adds; synthesis: fma), so both paths agree.
+// exchange partners with __shfl_xor(1) / (2).  Arithmetic: unnormalised butterflies on packed fp32 pairs
+// (see below); agrees with the general kernels to <= 1 LSB on < 0.2 % of the pixels (tests/test_gpu_wavelet.py).
 #include "b2d_denoise.cuh"
 #include "b2d_plan.h"
 #include "b2d_wavelet.cuh"
@@ -27,102 +27,109 @@
 
 namespace b2d {
 
-constexpr float HS = 0.70710678118654752f;          // 1 / sqrt(2) as the float the general path uses
+// ---------------------------------------------------------------------------------------------------------
+// Arithmetic.  Two things keep the instruction count down (both kernels are issue bound):
+//  * packed fp32 pairs (FADD2 / FMUL2 / FFMA2, one issue slot for two lanes' worth of IEEE fp32 operations): a pair
+//    holds pixels (k, k + 4) of a row, which makes every butterfly of level 1 (pairs of blocks i, i + 2) and the
+//    x-direction of level 2 (pairs j = 0, 1) a packed operation with no lane shuffling inside a register pair;
+//  * the UNNORMALISED Haar butterfly: pywt's a = (e + o) / sqrt 2, d = (e - o) / sqrt 2 applied along x and along y
+//    is (sums and differences of the 2 x 2 block) / 2, so level l coefficients are kept as 2^l times their value -
+//    pure additions - and the exact powers of two are folded into the thresholds (x 2^l), the band energies
+//    (x 4^-l), the stored dd_1 (x 1/2) and, on the way back, into one factor 1/4 per level and the colour matrix.
+//    Exact zeros stay exact ((a - b) - (c - d) cancels in any scaling), which is what _sigma_est_dwt looks at.
+// ---------------------------------------------------------------------------------------------------------
+typedef unsigned long long f2;                        // two fp32 in one 64-bit register pair
 
-struct HaarCoef {                                     // one channel of one lane (8 px x 2 rows)
-  float da[4], ad[4], dd[4];                          // level 1 (this lane's row of the 4 x 4 band)
-  float l2[4];                                        // even lane: aa2[2], ad2[2]; odd lane: da2[2], dd2[2]
-  float l3[2];                                        // r = 0: aa3, ad3;  r = 2: da3, dd3
-};
-
-// pywt dwt of the pair (even, odd): out = sum_j filt[j] * x[2 i + 1 - j], products and sums rounded separately
-__device__ __forceinline__ void an(float e, float o, float& a, float& d) {
-  a = __fadd_rn(__fmul_rn(HS, o), __fmul_rn(HS, e));
-  d = __fadd_rn(__fmul_rn(-HS, o), __fmul_rn(HS, e));
+__device__ __forceinline__ f2 pk(float lo, float hi) {
+  f2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
 }
-// pywt idwt of (a, d) -> (even, odd) samples, accumulated with fma like idwt_tap
-__device__ __forceinline__ void syn(float a, float d, float& e, float& o) {
-  const float sa = __fmul_rn(HS, a);
-  e = fmaf(HS, d, sa);
-  o = fmaf(-HS, d, sa);
+__device__ __forceinline__ void unpk(f2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f2 splat(float x) { return pk(x, x); }
+__device__ __forceinline__ f2 add2(f2 a, f2 b) {
+  f2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f2 sub2(f2 a, f2 b) {
+  f2 r;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) {
+  f2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) {
+  f2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ f2 add2_rz(f2 a, f2 b) {
+  f2 r;
+  asm("add.rz.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ float min3f(float a, float b, float c) {
+  float d;
+  asm("min.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+__device__ __forceinline__ float max3f(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+__device__ __forceinline__ float shx(float v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
+__device__ __forceinline__ f2 shx2(f2 v, int m) {
+  float lo, hi;
+  unpk(v, lo, hi);
+  return pk(shx(lo, m), shx(hi, m));
+}
+// pywt.threshold(d, t, 'soft') on both halves
+__device__ __forceinline__ f2 soft2(f2 v, float t) {
+  float lo, hi;
+  unpk(v, lo, hi);
+  return pk(wv_soft(lo, t), wv_soft(hi, t));
 }
 
-__device__ __forceinline__ void haar_forward(const float (&x0)[8], const float (&x1)[8], int r, HaarCoef& c) {
-  float aa1[4];
+// The 8 values of one Philox group on the reference's float scale ([0, 1] = [0, 255]), BEFORE any ->u8 cast: what
+// denoise_wavelet is fed (minibatch.py:91-94).  gaussian / speckle are the reference's own expressions in one
+// FFMA.SAT each - clip(f + n, 0, 1), clip(f + f n, 0, 1) with f = v / 255; the other operators go through their
+// general float view (b2d_noise.cuh).
+template <int KIND>
+__device__ __forceinline__ void unit8(const NoiseArgs& na, const GroupCtx& gc, uint2 w, float (&u)[8]) {
+  if constexpr (KIND == NK_GAUSSIAN || KIND == NK_SPECKLE) {
+    const uint4 r = group_random(na, gc, 0);
+    float n[8];
+    normal_pair(r.x, na.p0, n[0], n[1]);
+    normal_pair(r.y, na.p0, n[2], n[3]);
+    normal_pair(r.z, na.p0, n[4], n[5]);
+    normal_pair(r.w, na.p0, n[6], n[7]);
+    const float v[8] = {magic_byte<0>(w.x), magic_byte<1>(w.x), magic_byte<2>(w.x), magic_byte<3>(w.x),
+                        magic_byte<0>(w.y), magic_byte<1>(w.y), magic_byte<2>(w.y), magic_byte<3>(w.y)};
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    float lo0, hi0, lo1, hi1;
-    an(x0[2 * i], x0[2 * i + 1], lo0, hi0);
-    an(x1[2 * i], x1[2 * i + 1], lo1, hi1);
-    an(lo0, lo1, aa1[i], c.da[i]);
-    an(hi0, hi1, c.ad[i], c.dd[i]);
-  }
-  float aa2[2];
-  const bool odd = (r & 1) != 0;
-#pragma unroll
-  for (int j = 0; j < 2; ++j) {                       // level 2: rows r (even) and r + 1 (odd)
-    float lo, hi;
-    an(aa1[2 * j], aa1[2 * j + 1], lo, hi);
-    const float plo = __shfl_xor_sync(0xffffffffu, lo, 1), phi = __shfl_xor_sync(0xffffffffu, hi, 1);
-    float a, d, a2, d2;
-    an(odd ? plo : lo, odd ? lo : plo, a, d);         // from the row-low band: aa / da
-    an(odd ? phi : hi, odd ? hi : phi, a2, d2);       // from the row-high band: ad / dd
-    aa2[j] = a;
-    c.l2[j] = odd ? d : a;
-    c.l2[2 + j] = odd ? d2 : a2;
-  }
-  {                                                   // level 3: rows r = 0 (even) and r = 2 (odd)
-    float lo, hi;
-    an(aa2[0], aa2[1], lo, hi);
-    const float plo = __shfl_xor_sync(0xffffffffu, lo, 2), phi = __shfl_xor_sync(0xffffffffu, hi, 2);
-    const bool low = (r & 2) != 0;
-    float a, d, a2, d2;
-    an(low ? plo : lo, low ? lo : plo, a, d);
-    an(low ? phi : hi, low ? hi : phi, a2, d2);
-    c.l3[0] = low ? d : a;
-    c.l3[1] = low ? d2 : a2;
-  }
-}
-
-__device__ __forceinline__ float soft_thr(float d, float thr) { return wv_soft(d, thr); }
-
-// thr[level - 1][band], band 0 = da, 1 = ad, 2 = dd
-__device__ __forceinline__ void haar_inverse(const HaarCoef& c, int r, const float (&thr)[3][3], float (&x0)[8],
-                                             float (&x1)[8]) {
-  const bool odd = (r & 1) != 0, low = (r & 2) != 0;
-  float aa2[2];
-  {                                                   // level 3 -> aa2 (held by even lanes)
-    float t0, t1;                                     // r = 0: tlo = syn(aa3, ad3); r = 2: thi = syn(da3, dd3)
-    syn(low ? soft_thr(c.l3[0], thr[2][0]) : c.l3[0], soft_thr(c.l3[1], low ? thr[2][2] : thr[2][1]), t0, t1);
-    const float p0 = __shfl_xor_sync(0xffffffffu, t0, 2), p1 = __shfl_xor_sync(0xffffffffu, t1, 2);
-    float e, o;
-    syn(low ? p0 : t0, low ? t0 : p0, e, o);
-    aa2[0] = low ? o : e;
-    syn(low ? p1 : t1, low ? t1 : p1, e, o);
-    aa2[1] = low ? o : e;
-  }
-  float aa1[4];
-  {                                                   // level 2 -> aa1 (one row of 4 per lane)
-    float t[4];
-#pragma unroll
-    for (int j = 0; j < 2; ++j)                       // even: syn(aa2, ad2) = tlo; odd: syn(da2, dd2) = thi
-      syn(odd ? soft_thr(c.l2[j], thr[1][0]) : aa2[j], soft_thr(c.l2[2 + j], odd ? thr[1][2] : thr[1][1]), t[2 * j],
-          t[2 * j + 1]);
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const float p = __shfl_xor_sync(0xffffffffu, t[k], 1);
-      float e, o;
-      syn(odd ? p : t[k], odd ? t[k] : p, e, o);
-      aa1[k] = odd ? o : e;
+    for (int i = 0; i < 8; ++i) {
+      const float b = v[i] - 8388608.0f;              // the byte as a float, exact
+      if (KIND == NK_GAUSSIAN) u[i] = __saturatef(fmaf(b, 1.0f / 255.0f, n[i]));
+      else {
+        const float f = b * (1.0f / 255.0f);
+        u[i] = __saturatef(fmaf(f, n[i], f));
+      }
     }
-  }
+  } else {
+    uint32_t v[8];
+    float f[8];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {                       // level 1, local
-    float tlo0, tlo1, thi0, thi1;
-    syn(aa1[i], soft_thr(c.ad[i], thr[0][1]), tlo0, tlo1);
-    syn(soft_thr(c.da[i], thr[0][0]), soft_thr(c.dd[i], thr[0][2]), thi0, thi1);
-    syn(tlo0, thi0, x0[2 * i], x1[2 * i]);
-    syn(tlo1, thi1, x0[2 * i + 1], x1[2 * i + 1]);
+    for (int i = 0; i < 4; ++i) {
+      v[i] = (w.x >> (8 * i)) & 0xffu;
+      v[4 + i] = (w.y >> (8 * i)) & 0xffu;
+    }
+    apply8_float<KIND, NM_GEN>(na, gc, v, f);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) u[i] = f[i] * (1.0f / 255.0f);
   }
 }
 
@@ -137,12 +144,12 @@ struct HaarGeom {
   size_t dd_floats;           // (H / 2) * (W / 2)
 };
 
-// Loads this lane's 8 px x 2 rows, applies the noise operator and converts to the three
-// "YCbCr" channels: P[c][row][x].  Lanes right of the image (ragged last strip) shadow block
-// bw - 1 so that the shuffles stay convergent; `live` tells whether the lane owns real pixels.
+// Loads this lane's 8 px x 2 rows, applies the noise operator and converts to the three "YCbCr" channels:
+// P[c][row][k] = (pixel k, pixel k + 4), k = 0..3.  Lanes right of the image (ragged last strip) shadow block bw - 1
+// so that the shuffles stay convergent; `live` tells whether the lane owns real pixels.
 template <int KIND>
 __device__ __forceinline__ void haar_load(const ImageSet& s, const NoiseArgs& na, const uint8_t* img, int img_local,
-                                          int px0, int y0, float (&P)[3][2][8]) {
+                                          int px0, int y0, f2 (&P)[3][2][4]) {
 #pragma unroll
   for (int row = 0; row < 2; ++row) {
     const uint32_t byte0 = (uint32_t)(y0 + row) * (uint32_t)s.rowbytes + (uint32_t)px0 * 3u;   // multiple of 24
@@ -150,113 +157,177 @@ __device__ __forceinline__ void haar_load(const ImageSet& s, const NoiseArgs& na
     float xf[24];
 #pragma unroll
     for (int q = 0; q < 3; ++q) {
-      const uint2 w = __ldg(src + q);
-      uint32_t v[8];
-      float f[8];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        v[i] = (w.x >> (8 * i)) & 0xffu;
-        v[4 + i] = (w.y >> (8 * i)) & 0xffu;
-      }
+      float u[8];
       GroupCtx gc{(uint32_t)img_local, byte0 / 8u + (uint32_t)q, img};
-      apply8_float<KIND, NM_GEN>(na, gc, v, f);
+      unit8<KIND>(na, gc, __ldg(src + q), u);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) xf[8 * q + i] = f[i] * (1.0f / 255.0f);
+      for (int i = 0; i < 8; ++i) xf[8 * q + i] = u[i];
     }
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const float c0 = xf[3 * k], c1 = xf[3 * k + 1], c2 = xf[3 * k + 2];
+    for (int k = 0; k < 4; ++k) {
+      const f2 c0 = pk(xf[3 * k], xf[3 * k + 12]), c1 = pk(xf[3 * k + 1], xf[3 * k + 13]), c2 = pk(xf[3 * k + 2], xf[3 * k + 14]);
 #pragma unroll
       for (int c = 0; c < 3; ++c)
-        P[c][row][k] = kHaarYCC[c][0] * c0 + kHaarYCC[c][1] * c1 + kHaarYCC[c][2] * c2 + (c == 0 ? 16.0f : 128.0f);
+        P[c][row][k] = fma2(splat(kHaarYCC[c][2]), c2,
+                            fma2(splat(kHaarYCC[c][1]), c1, fma2(splat(kHaarYCC[c][0]), c0, splat(c == 0 ? 16.0f : 128.0f))));
     }
   }
+}
+
+// One channel of one lane (8 px x 2 rows) after the forward transform, unnormalised (level l values x 2^l).
+struct HaarCoef {
+  f2 da[2], ad[2], dd[2];      // level 1: pair m holds blocks i = m and i = m + 2 of this lane's row of the 4 x 4 band
+  f2 aa2, ad2, da2, dd2;       // level 2, pairs over j = 0, 1.  aa2: every lane; ad2: valid on even lanes; da2, dd2: on odd lanes
+  float aa3, ad3, da3, dd3;    // level 3.  aa3, ad3: valid on lane r = 0; da3, dd3: on lane r = 2
+};
+
+__device__ __forceinline__ void haar_forward(const f2 (&P)[2][4], HaarCoef& c) {
+  f2 a1[2];
+#pragma unroll
+  for (int m = 0; m < 2; ++m) {                       // x: pixel pairs (2 m, 2 m + 1) = blocks i = m (low half), m + 2 (high half)
+    const f2 s0 = add2(P[0][2 * m], P[0][2 * m + 1]), d0 = sub2(P[0][2 * m], P[0][2 * m + 1]);
+    const f2 s1 = add2(P[1][2 * m], P[1][2 * m + 1]), d1 = sub2(P[1][2 * m], P[1][2 * m + 1]);
+    a1[m] = add2(s0, s1);                             // y: rows 0 / 1
+    c.da[m] = sub2(s0, s1);
+    c.ad[m] = add2(d0, d1);
+    c.dd[m] = sub2(d0, d1);
+  }
+  // level 2: this lane's row of aa1 is (a1[0].lo, a1[1].lo, a1[0].hi, a1[1].hi); x pairs (2 j, 2 j + 1) -> j = 0, 1 packed.
+  // Rows r (even lane) and r + 1 (odd lane): e = the even lane's value, o = the odd lane's; the difference bands are
+  // written as (partner - own), which is e - o on the odd lanes - the ones that keep them.
+  const f2 lo = add2(a1[0], a1[1]), hi = sub2(a1[0], a1[1]);
+  const f2 plo = shx2(lo, 1), phi = shx2(hi, 1);
+  c.aa2 = add2(lo, plo);
+  c.da2 = sub2(plo, lo);
+  c.ad2 = add2(hi, phi);
+  c.dd2 = sub2(phi, hi);
+  // level 3: rows r = 0 (e) and r = 2 (o) of aa2; same convention, difference bands valid on the r = 2 lane
+  float x0, x1;
+  unpk(c.aa2, x0, x1);
+  const float lo3 = x0 + x1, hi3 = x0 - x1;
+  const float plo3 = shx(lo3, 2), phi3 = shx(hi3, 2);
+  c.aa3 = lo3 + plo3;
+  c.da3 = plo3 - lo3;
+  c.ad3 = hi3 + phi3;
+  c.dd3 = phi3 - hi3;
 }
 
 // ------------------------------------------------------------------ pass A
 template <int KIND>
 __global__ void __launch_bounds__(256, 2) k_haar_stats(ImageSet s, NoiseArgs na, HaarGeom hg, float* dd1, WvStats* stats,
-                                                        int chunk_first) {
+                                                        unsigned int* hist, int chunk_first) {
+  // pass 0 of the radix select (bits 30..20 of |dd_1|, zeros skipped: k_select_hist's rule) is tallied here, while the
+  // coefficients are in registers: one full read of the band less (wavelet_sigma_thresholds(..., first_pass = 1))
+  __shared__ unsigned int s_hist[3][WV_BINS];
+  for (int i = threadIdx.x; i < 3 * WV_BINS; i += 256) (&s_hist[0][0])[i] = 0u;
+  __syncthreads();
   const int z = blockIdx.y;
   const int img_local = image_of(s, chunk_first + z);
   const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
   const int lane = threadIdx.x & 31, r = lane & 3, bxw = lane >> 2;
   const int warp = blockIdx.x * 8 + (threadIdx.x >> 5), nwarps = gridDim.x * 8;
-  float mn[3], mx[3], en[3][3][3];                    // en[channel][level - 1][band]
+  // sums of squares of the UNNORMALISED coefficients, accumulated on every lane; the lanes that do not own a band
+  // (see HaarCoef) are masked out once, after the loop
+  float mn[3], mx[3], e3[3][3];
+  f2 e1[3][3], e2[3][3];                              // [channel][band: 0 = da, 1 = ad, 2 = dd]
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
     mn[c] = 3.0e38f;
     mx[c] = -3.0e38f;
 #pragma unroll
-    for (int l = 0; l < 3; ++l)
-#pragma unroll
-      for (int b = 0; b < 3; ++b) en[c][l][b] = 0.f;
+    for (int b = 0; b < 3; ++b) {
+      e1[c][b] = e2[c][b] = splat(0.f);
+      e3[c][b] = 0.f;
+    }
   }
-  const bool odd = (r & 1) != 0, low = (r & 2) != 0;
   for (int strip = warp; strip < hg.total_strips; strip += nwarps) {
     const int by = strip / hg.strips_x, sx = strip - by * hg.strips_x;
     const int bx_raw = sx * 8 + bxw;
     const bool live = bx_raw < hg.bw;
     const int bx = live ? bx_raw : hg.bw - 1;
-    float P[3][2][8];
+    f2 P[3][2][4];
     haar_load<KIND>(s, na, img, img_local, bx * 8, by * 8 + 2 * r, P);
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
       HaarCoef k;
-      haar_forward(P[c][0], P[c][1], r, k);
+      haar_forward(P[c], k);
       if (!live) continue;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        mn[c] = fminf(mn[c], fminf(P[c][0][i], P[c][1][i]));
-        mx[c] = fmaxf(mx[c], fmaxf(P[c][0][i], P[c][1][i]));
-      }
+      for (int row = 0; row < 2; ++row)
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        en[c][0][0] = fmaf(k.da[i], k.da[i], en[c][0][0]);
-        en[c][0][1] = fmaf(k.ad[i], k.ad[i], en[c][0][1]);
-        en[c][0][2] = fmaf(k.dd[i], k.dd[i], en[c][0][2]);
-      }
+        for (int i = 0; i < 4; ++i) {
+          float a, b;
+          unpk(P[c][row][i], a, b);
+          mn[c] = min3f(mn[c], a, b);
+          mx[c] = max3f(mx[c], a, b);
+        }
 #pragma unroll
-      for (int j = 0; j < 2; ++j) {                   // even lanes: (aa2, ad2); odd lanes: (da2, dd2)
-        const float a = k.l2[j] * k.l2[j], b = k.l2[2 + j] * k.l2[2 + j];
-        en[c][1][0] += odd ? a : 0.f;
-        en[c][1][1] += odd ? 0.f : b;
-        en[c][1][2] += odd ? b : 0.f;
+      for (int m = 0; m < 2; ++m) {
+        e1[c][0] = fma2(k.da[m], k.da[m], e1[c][0]);
+        e1[c][1] = fma2(k.ad[m], k.ad[m], e1[c][1]);
+        e1[c][2] = fma2(k.dd[m], k.dd[m], e1[c][2]);
       }
-      if (!odd) {                                     // r = 0: (aa3, ad3); r = 2: (da3, dd3)
-        const float a = k.l3[0] * k.l3[0], b = k.l3[1] * k.l3[1];
-        en[c][2][0] += low ? a : 0.f;
-        en[c][2][1] += low ? 0.f : b;
-        en[c][2][2] += low ? b : 0.f;
-      }
+      e2[c][0] = fma2(k.da2, k.da2, e2[c][0]);
+      e2[c][1] = fma2(k.ad2, k.ad2, e2[c][1]);
+      e2[c][2] = fma2(k.dd2, k.dd2, e2[c][2]);
+      e3[c][0] = fmaf(k.da3, k.da3, e3[c][0]);
+      e3[c][1] = fmaf(k.ad3, k.ad3, e3[c][1]);
+      e3[c][2] = fmaf(k.dd3, k.dd3, e3[c][2]);
+      // dd_1 itself (x 1/2: exact) for the median: blocks i = 0..3 of this lane's row of the band
+      float d0, d2, d1, d3;
+      unpk(mul2(k.dd[0], splat(0.5f)), d0, d2);
+      unpk(mul2(k.dd[1], splat(0.5f)), d1, d3);
       float4* dst = reinterpret_cast<float4*>(dd1 + ((size_t)z * 3 + c) * hg.dd_floats +
                                               (size_t)(by * 4 + r) * hg.w2 + (size_t)bx * 4);
-      *dst = make_float4(k.dd[0], k.dd[1], k.dd[2], k.dd[3]);
+      *dst = make_float4(d0, d1, d2, d3);
+      const unsigned int b0 = __float_as_uint(d0) & 0x7fffffffu, b1 = __float_as_uint(d1) & 0x7fffffffu;
+      const unsigned int b2 = __float_as_uint(d2) & 0x7fffffffu, b3 = __float_as_uint(d3) & 0x7fffffffu;
+      if (b0) atomicAdd(&s_hist[c][b0 >> 20], 1u);
+      if (b1) atomicAdd(&s_hist[c][b1 >> 20], 1u);
+      if (b2) atomicAdd(&s_hist[c][b2 >> 20], 1u);
+      if (b3) atomicAdd(&s_hist[c][b3 >> 20], 1u);
     }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 3 * WV_BINS; i += 256) {
+    const unsigned int v = (&s_hist[0][0])[i];
+    if (v) atomicAdd(&hist[((size_t)z * 3 + i / WV_BINS) * 2 * WV_BINS + (i % WV_BINS)], v);
   }
   __shared__ double s_en[27];
   __shared__ int s_mn[3], s_mx[3];
   if (threadIdx.x < 27) s_en[threadIdx.x] = 0.0;
   if (threadIdx.x < 3) { s_mn[threadIdx.x] = 0x7fffffff; s_mx[threadIdx.x] = (int)0x80000000; }
   __syncthreads();
+  const bool odd = (r & 1) != 0;
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
     for (int o = 16; o; o >>= 1) {
-      mn[c] = fminf(mn[c], __shfl_xor_sync(0xffffffffu, mn[c], o));
-      mx[c] = fmaxf(mx[c], __shfl_xor_sync(0xffffffffu, mx[c], o));
+      mn[c] = fminf(mn[c], shx(mn[c], o));
+      mx[c] = fmaxf(mx[c], shx(mx[c], o));
     }
     if (lane == 0) {
       atomicMin(&s_mn[c], f2ord(mn[c]));
       atomicMax(&s_mx[c], f2ord(mx[c]));
     }
 #pragma unroll
-    for (int l = 0; l < 3; ++l)
-#pragma unroll
-      for (int b = 0; b < 3; ++b) {
-        float e = en[c][l][b];
-        for (int o = 16; o; o >>= 1) e += __shfl_xor_sync(0xffffffffu, e, o);
-        if (lane == 0) atomicAdd(&s_en[(c * 3 + l) * 3 + b], (double)e);
+    for (int b = 0; b < 3; ++b) {
+      float a, bb;
+      unpk(e1[c][b], a, bb);
+      float v1 = 0.25f * (a + bb);                                   // level 1: every lane owns its row; (x / 2)^2
+      unpk(e2[c][b], a, bb);
+      float v2 = ((b == 1) != odd) ? 0.0625f * (a + bb) : 0.f;       // level 2: ad on even lanes, da / dd on odd lanes; (x / 4)^2
+      float v3 = (r == (b == 1 ? 0 : 2)) ? 0.015625f * e3[c][b] : 0.f;   // level 3: ad on r = 0, da / dd on r = 2; (x / 8)^2
+      for (int o = 16; o; o >>= 1) {
+        v1 += shx(v1, o);
+        v2 += shx(v2, o);
+        v3 += shx(v3, o);
       }
+      if (lane == 0) {
+        atomicAdd(&s_en[(c * 3 + 0) * 3 + b], (double)v1);
+        atomicAdd(&s_en[(c * 3 + 1) * 3 + b], (double)v2);
+        atomicAdd(&s_en[(c * 3 + 2) * 3 + b], (double)v3);
+      }
+    }
   }
   __syncthreads();
   if (threadIdx.x < 27) {
@@ -270,6 +341,33 @@ __global__ void __launch_bounds__(256, 2) k_haar_stats(ImageSet s, NoiseArgs na,
 }
 
 // ------------------------------------------------------------------ pass B
+// T[level - 1][band] = threshold x 2^level (the coefficients are unnormalised); band 0 = da, 1 = ad, 2 = dd.
+// Q = 4 x the reconstructed channel values, same pairing as P.
+__device__ __forceinline__ void haar_inverse(const HaarCoef& c, bool odd, bool low, const float (&T)[3][3], f2 (&Q)[2][4]) {
+  // level 3 -> aa2: lane r = 0 synthesises (aa3, ad3) along x, lane r = 2 (da3, dd3); then rows e / o along y
+  const float first3 = low ? wv_soft(c.da3, T[2][0]) : c.aa3;
+  const float second3 = wv_soft(low ? c.dd3 : c.ad3, low ? T[2][2] : T[2][1]);
+  const f2 t3 = pk(first3 + second3, first3 - second3);
+  const f2 aa2 = fma2(t3, splat(low ? -0.25f : 0.25f), mul2(shx2(t3, 2), splat(0.25f)));   // r = 0: (t + p) / 4; r = 2: (p - t) / 4
+  // level 2 -> aa1: even lanes synthesise (aa2, ad2), odd lanes (da2, dd2)
+  const f2 first2 = odd ? soft2(c.da2, T[1][0]) : aa2;
+  const f2 second2 = soft2(odd ? c.dd2 : c.ad2, odd ? T[1][2] : T[1][1]);
+  const f2 tE = add2(first2, second2), tO = sub2(first2, second2);
+  const f2 sg = splat(odd ? -0.25f : 0.25f), q = splat(0.25f);
+  f2 a1[2];
+  a1[0] = fma2(tE, sg, mul2(shx2(tE, 1), q));          // blocks i = 0, 2
+  a1[1] = fma2(tO, sg, mul2(shx2(tO, 1), q));          // blocks i = 1, 3
+#pragma unroll
+  for (int m = 0; m < 2; ++m) {                        // level 1, local
+    const f2 ad = soft2(c.ad[m], T[0][1]), da = soft2(c.da[m], T[0][0]), dd = soft2(c.dd[m], T[0][2]);
+    const f2 tlo0 = add2(a1[m], ad), tlo1 = sub2(a1[m], ad), thi0 = add2(da, dd), thi1 = sub2(da, dd);
+    Q[0][2 * m] = add2(tlo0, thi0);
+    Q[1][2 * m] = sub2(tlo0, thi0);
+    Q[0][2 * m + 1] = add2(tlo1, thi1);
+    Q[1][2 * m + 1] = sub2(tlo1, thi1);
+  }
+}
+
 __device__ __forceinline__ uint32_t pack_low_bytes(uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   return __byte_perm(__byte_perm(a, b, 0x0040), __byte_perm(c, d, 0x0040), 0x5410);
 }
@@ -285,46 +383,64 @@ __global__ void __launch_bounds__(256, 2) k_haar_apply(ImageSet s, NoiseArgs na,
   uint8_t* out = s.out + (uint64_t)img_local * s.elems;
   const int lane = threadIdx.x & 31, r = lane & 3, bxw = lane >> 2;
   const int warp = blockIdx.x * 8 + (threadIdx.x >> 5), nwarps = gridDim.x * 8;
-  float thr[3][3][3], lo[3], hi[3];
+  const bool odd = (r & 1) != 0, low = (r & 2) != 0;
+  float T[3][3][3], lo4[3], hi4[3], inv4[3][3], k0[3];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
     const WvStats& st = stats[z * 3 + c];
-    lo[c] = st.lo;
-    hi[c] = st.hi;
+    lo4[c] = 4.0f * st.lo;                             // Q = 4 x value: the clip range and the offsets scale with it (exact)
+    hi4[c] = 4.0f * st.hi;
 #pragma unroll
     for (int l = 0; l < 3; ++l)
 #pragma unroll
-      for (int b = 0; b < 3; ++b) thr[c][l][b] = st.thr[l + 1][b];
+      for (int b = 0; b < 3; ++b) T[c][l][b] = st.thr[l + 1][b] * (float)(2 << l);
+  }
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+#pragma unroll
+    for (int j = 0; j < 3; ++j) inv4[c][j] = 0.25f * fa.inv[c][j];
+    // ycbcr2rgb subtracts (16, 128, 128) first; here the offsets ride in the chain's first addend
+    k0[c] = -(inv4[c][0] * 64.0f + inv4[c][1] * 512.0f + inv4[c][2] * 512.0f);
   }
   for (int strip = warp; strip < hg.total_strips; strip += nwarps) {
     const int by = strip / hg.strips_x, sx = strip - by * hg.strips_x;
     const int bx_raw = sx * 8 + bxw;
     const bool live = bx_raw < hg.bw;
     const int bx = live ? bx_raw : hg.bw - 1;
-    float P[3][2][8];
+    f2 P[3][2][4];
     haar_load<KIND>(s, na, img, img_local, bx * 8, by * 8 + 2 * r, P);
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
       HaarCoef k;
-      haar_forward(P[c][0], P[c][1], r, k);
-      haar_inverse(k, r, thr[c], P[c][0], P[c][1]);
+      haar_forward(P[c], k);
+      haar_inverse(k, odd, low, T[c], P[c]);
+      // the per-channel denoise_wavelet clips to the channel's own [min, max] (its normalised [0, 1])
+#pragma unroll
+      for (int row = 0; row < 2; ++row)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float a, b;
+          unpk(P[c][row][i], a, b);
+          P[c][row][i] = pk(fminf(fmaxf(a, lo4[c]), hi4[c]), fminf(fmaxf(b, lo4[c]), hi4[c]));
+        }
     }
     if (!live) continue;
 #pragma unroll
     for (int row = 0; row < 2; ++row) {
       uint32_t o[24];                                   // 2^23 + byte as fp32 bits: the low byte is the result
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        // the per-channel denoise_wavelet clips to the channel's own [min, max] (its normalised [0, 1])
-        const float y = fminf(fmaxf(P[0][row][i], lo[0]), hi[0]) - 16.0f;
-        const float cb = fminf(fmaxf(P[1][row][i], lo[1]), hi[1]) - 128.0f;
-        const float cr = fminf(fmaxf(P[2][row][i], lo[2]), hi[2]) - 128.0f;
+      for (int i = 0; i < 4; ++i) {
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-          float v = fa.inv[c][0] * y + fa.inv[c][1] * cb + fa.inv[c][2] * cr;
-          v = fminf(fmaxf(v, 0.0f), 1.0f);
-          // (uint8)(255 * v): product rounded as the general path does, then truncated by the magic add
-          o[3 * i + c] = __float_as_uint(__fadd_rz(__fmul_rn(255.0f, v), 8388608.0f));
+          const f2 v = fma2(splat(inv4[c][2]), P[2][row][i],
+                            fma2(splat(inv4[c][1]), P[1][row][i], fma2(splat(inv4[c][0]), P[0][row][i], splat(k0[c]))));
+          float a, b;
+          unpk(v, a, b);
+          // (uint8)(255 * clip(v, 0, 1)): product rounded as the general path does, then truncated by the magic add
+          const f2 t = add2_rz(mul2(pk(__saturatef(a), __saturatef(b)), splat(255.0f)), splat(8388608.0f));
+          unpk(t, a, b);
+          o[3 * i + c] = __float_as_uint(a);            // pixel i
+          o[3 * (i + 4) + c] = __float_as_uint(b);      // pixel i + 4
         }
       }
       const uint32_t byte0 = (uint32_t)(by * 8 + 2 * r + row) * (uint32_t)s.rowbytes + (uint32_t)bx * 24u;
@@ -348,15 +464,15 @@ bool haar_supported(const b2d_plan& p, const b2d_spec& sp, int mode) {
 
 template <int KIND>
 static void launch_haar(int which, dim3 grid, cudaStream_t st, const ImageSet& s, const NoiseArgs& na, const HaarGeom& hg,
-                        float* dd1, WvStats* stats, const HaarFinal& fa, int first) {
-  if (which == 0) k_haar_stats<KIND><<<grid, 256, 0, st>>>(s, na, hg, dd1, stats, first);
+                        float* dd1, WvStats* stats, unsigned int* hist, const HaarFinal& fa, int first) {
+  if (which == 0) k_haar_stats<KIND><<<grid, 256, 0, st>>>(s, na, hg, dd1, stats, hist, first);
   else k_haar_apply<KIND><<<grid, 256, 0, st>>>(s, na, hg, stats, fa, first);
 }
 
 static int dispatch_haar(int kind, int which, dim3 grid, cudaStream_t st, const ImageSet& s, const NoiseArgs& na,
-                         const HaarGeom& hg, float* dd1, WvStats* stats, const HaarFinal& fa, int first) {
+                         const HaarGeom& hg, float* dd1, WvStats* stats, unsigned int* hist, const HaarFinal& fa, int first) {
   switch (kind) {
-#define B2D_HAAR_CASE(K) case K: launch_haar<K>(which, grid, st, s, na, hg, dd1, stats, fa, first); break;
+#define B2D_HAAR_CASE(K) case K: launch_haar<K>(which, grid, st, s, na, hg, dd1, stats, hist, fa, first); break;
     B2D_HAAR_CASE(NK_NONE) B2D_HAAR_CASE(NK_GAUSSIAN) B2D_HAAR_CASE(NK_SPECKLE) B2D_HAAR_CASE(NK_SAP)
     B2D_HAAR_CASE(NK_POISSON) B2D_HAAR_CASE(NK_UNIFORM) B2D_HAAR_CASE(NK_RAYLEIGH) B2D_HAAR_CASE(NK_GAMMA)
     B2D_HAAR_CASE(NK_TABLE_ADD) B2D_HAAR_CASE(NK_SHADER)
@@ -410,10 +526,10 @@ int run_haar(const b2d_plan& p, const ImageSet& s, int kind, const NoiseArgs& na
     }
     const dim3 grid((unsigned)per_image, (unsigned)cnt, 1);
     wavelet_stats_begin(stats, hist, cnt * 3, st);
-    int rc = dispatch_haar(kind, 0, grid, st, s, na, hg, dd1, stats, fa, first);
+    int rc = dispatch_haar(kind, 0, grid, st, s, na, hg, dd1, stats, hist, fa, first);
     if (rc) return rc;
-    wavelet_sigma_thresholds(g, dd1, stats, hist, cnt * 3, st);
-    rc = dispatch_haar(kind, 1, grid, st, s, na, hg, dd1, stats, fa, first);
+    wavelet_sigma_thresholds(g, dd1, stats, hist, cnt * 3, st, 1);        // pass 0's histogram is already in `hist`
+    rc = dispatch_haar(kind, 1, grid, st, s, na, hg, dd1, stats, hist, fa, first);
     if (rc) return rc;
     p.wv_stats_dev = stats; p.wv_stats_first = first; p.wv_stats_count = cnt;
     const cudaError_t e = cudaGetLastError();

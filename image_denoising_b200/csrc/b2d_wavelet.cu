@@ -872,12 +872,15 @@ void wavelet_stats_begin(WvStats* stats, unsigned int* hist, int planes, cudaStr
 }
 
 void wavelet_sigma_thresholds(const WvGeom& g, const float* ws, WvStats* stats, unsigned int* hist, int planes,
-                              cudaStream_t st) {
+                              cudaStream_t st, int first_pass) {
   auto blocks = [](size_t n) { return (unsigned)std::min<size_t>((n + 255) / 256, 148 * 8); };
   for (int pass = 0; pass < 3; ++pass) {
-    k_select_hist<<<dim3(std::min(blocks((size_t)g.h[1] * g.w[1]), 32u), 1, planes), 256, 0, st>>>(g, ws, stats, hist, pass);
+    if (pass >= first_pass) {                             // else: the caller's kernel has tallied this pass already
+      k_select_hist<<<dim3(std::min(blocks((size_t)g.h[1] * g.w[1]), 32u), 1, planes), 256, 0, st>>>(g, ws, stats, hist, pass);
+      count_launch();
+    }
     k_select_step<<<planes, 256, 0, st>>>(stats, hist, pass);
-    count_launch(); count_launch();
+    count_launch();
   }
   k_thresholds<<<(planes + 63) / 64, 64, 0, st>>>(g, stats, planes);
   count_launch();

@@ -46,8 +46,9 @@ __device__ __forceinline__ float wv_soft(float d, float thr) { return copysignf(
 // shared between the general path (b2d_wavelet.cu) and the Haar fast path (b2d_haar.cu)
 void wavelet_stats_begin(WvStats* stats, unsigned int* hist, int planes, cudaStream_t st);
 // median(|dd_1| != 0) -> sigma, then the BayesShrink thresholds; dd_1 of plane z at ws + z * g.chan_floats + g.off_det[1][2]
+// first_pass = 1: the histogram of radix pass 0 (bits 30..20, hist[plane][0][*]) has been filled by the caller
 void wavelet_sigma_thresholds(const WvGeom& g, const float* ws, WvStats* stats, unsigned int* hist, int planes,
-                              cudaStream_t st);
+                              cudaStream_t st, int first_pass = 0);
 #endif
 
 }  // namespace b2d

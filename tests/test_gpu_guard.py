@@ -61,9 +61,9 @@ def test_no_write_outside_the_output_and_runs_repeat(cuda, shape, offset):
             aligned = plan.run(src, seed=5, first_index=2)
             if kw.get("wavelet") == "db1" and h % 8 == 0 and w % 8 == 0:
                 # the register-resident Haar path needs 8-byte aligned bases; an odd base runs the general path, which
-                # agrees with it to <= 1 LSB on < 0.2 % of the pixels (tests/test_gpu_wavelet.py)
+                # agrees with it to <= 1 LSB on < 1 % of the pixels (tests/test_gpu_wavelet.py)
                 d = (aligned.int() - first.int()).abs()
-                if int(d.max()) > 1 or float((d > 0).float().mean()) > 2e-3:
+                if int(d.max()) > 1 or float((d > 0).float().mean()) > 1e-2:
                     bad.append((spec, kw, "general vs Haar path", int(d.max()), float((d > 0).float().mean())))
             elif not torch.equal(aligned, first):
                 bad.append((spec, kw, "unaligned base differs from aligned", int((aligned != first).sum())))

@@ -99,7 +99,10 @@ np.savez(sys.argv[2], **out)
 def test_haar_fast_path_equals_general_path(cuda, tmp_path):
     """Generator mode, every noise operator: the register-resident db1 / 3-level path (b2d_haar.cu)
     against the general multi-pass path (B2D_HAAR=0) of the same library, same Philox counters.
-    Both compute fp32 with the same operation order; only the band energies are summed differently."""
+    Both are fp32 but round differently (the fast path runs unnormalised butterflies on packed pairs and takes the
+    reference's clip(f + n, 0, 1) in one FFMA.SAT); each is held to the oracle on its own (stage-wise tests above), this
+    is only a cross-check: <= 1 LSB, on < 1 % of the pixels (at these noise levels many outputs sit exactly on an
+    integer, where the last bit of either path decides the truncation)."""
     import os
     import subprocess
     import sys
@@ -113,7 +116,7 @@ def test_haar_fast_path_equals_general_path(cuda, tmp_path):
     assert set(outs["fast"]) == set(outs["general"]) and len(outs["fast"]) == 2 * len(_HAAR_SPECS), sorted(outs["fast"])
     for key, a in outs["fast"].items():
         d = np.abs(a.astype(int) - outs["general"][key].astype(int))
-        assert d.max() <= 1 and (d > 0).mean() < 2e-3, (key, d.max(), (d > 0).mean())
+        assert d.max() <= 1 and (d > 0).mean() < 1e-2, (key, d.max(), (d > 0).mean())
 
 
 def test_specialised_wavelet_kernels_equal_generic(cuda, tmp_path):
