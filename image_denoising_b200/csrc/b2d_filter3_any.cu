@@ -24,13 +24,17 @@
 namespace b2d {
 
 constexpr int FA_THREADS = 256;
-constexpr int FA_TWB = 1024;               // tile width in bytes (one word per thread and row)
-constexpr int FA_TH = 32;                  // tile height in rows
-constexpr int FA_APRON = 16;               // shared bytes left of the tile (8 are loaded, 3 are used)
-constexpr int FA_SROW = FA_TWB + 32;
-constexpr int FA_ROWS = FA_TH + 2;
-constexpr int FA_XW = 3;                   // words per row past the first 256: [c0 - 8, c0 + 1028) is loaded
-constexpr size_t FA_SMEM = (size_t)FA_ROWS * FA_SROW + (size_t)FA_TH * FA_TWB;
+constexpr int FA_XW = 3;                   // words per row past the tile's own: [c0 - 8, c0 + TWB + 4) is loaded
+// Tile geometry: TWB bytes x (32 KiB / TWB) rows - 1024 x 32, 512 x 64 or 256 x 128.  Same shared memory, same 8-row
+// (median: 16-row) bands for all three; the launcher takes the width that pads a row least: 1125-byte rows (W = 375, the
+// reference's portrait VOC images) fill 5 tiles of 256 to 88 %, but 2 tiles of 1024 only to 55 %.
+template <int TWB>
+struct FaGeom {
+  static constexpr int TH = 32768 / TWB;
+  static constexpr int SROW = TWB + 32;
+  static constexpr int ROWS = TH + 2;
+  static constexpr size_t SMEM = (size_t)ROWS * SROW + (size_t)TH * TWB;
+};
 
 // the aligned word at p, bytes outside [lo, hi) read as 0
 __device__ __forceinline__ uint32_t guarded_word(const uint8_t* p, const uint8_t* lo, const uint8_t* hi) {
@@ -42,9 +46,11 @@ __device__ __forceinline__ uint32_t guarded_word(const uint8_t* p, const uint8_t
   return v;
 }
 
-template <int FILTER, int KW>
+template <int FILTER, int KW, int FA_TWB>
 __global__ void __launch_bounds__(FA_THREADS, 3) k_filter3_tile_any(ImageSet s) {
   using F = Filter3W<FILTER, KW>;
+  constexpr int FA_TH = FaGeom<FA_TWB>::TH, FA_SROW = FaGeom<FA_TWB>::SROW, FA_ROWS = FaGeom<FA_TWB>::ROWS;
+  static_assert(FA_ROWS <= FA_THREADS, "one thread per tile row builds the border pixels");
   constexpr int TPB = FA_TWB / (4 * KW);            // threads per band
   constexpr int BANDS = FA_THREADS / TPB;
   constexpr int BAND_H = FA_TH / BANDS;
@@ -59,42 +65,42 @@ __global__ void __launch_bounds__(FA_THREADS, 3) k_filter3_tile_any(ImageSet s) 
   const uint8_t* img_end = img + s.elems;
   const int rows = min(FA_ROWS, s.h - y0 + 2);      // tile row tr holds image row y0 - 1 + tr
 
-  // ---- load: bytes [c0 - 8, c0 + 1028) of every tile row, re-aligned to the shared row ----
-  auto row_src = [&](int tr) {
+  // ---- load: bytes [c0 - 8, c0 + TWB + 4) of every tile row, copied RAW in aligned 16-byte chunks ----
+  auto row_y = [&](int tr) {
     int ys = y0 - 1 + tr;
     if (ys < 0 || ys >= s.h) ys = border_map(ys, s.h, F::BORDER);
-    return img + (int64_t)ys * s.rowbytes + c0 - 8;                          // lands at shared offset APRON - 8
+    return ys;
   };
-  // phase (address & 3) of tile row tr, in 32-bit arithmetic: (base + ys * rowbytes) mod 4
-  const unsigned ph_base = (unsigned)((reinterpret_cast<uintptr_t>(img) + (unsigned)c0 - 8u) & 3u);
-  const unsigned rb3 = (unsigned)s.rowbytes & 3u;
-  auto row_phase = [&](int tr) {
-    int ys = y0 - 1 + tr;
-    if (ys < 0 || ys >= s.h) ys = border_map(ys, s.h, F::BORDER);
-    return (ph_base + ((unsigned)ys & 3u) * rb3) & 3u;
-  };
-  // A WARP owns a tile row (rows warp, warp + 8, ...): the aligned words that cover it go to shared
-  // memory RAW with 4-byte cp.async - every row of the tile is in flight at once, nothing waits in
-  // registers (ncu r01i: the register version sat 15 of 25 cycles per instruction on the loads at
-  // 37 % occupancy).  The row's phase (address & 3) is applied by the readers below.
-  constexpr int NW = FA_TWB / 4 + FA_XW + 1;        // aligned words per tile row (one more than re-aligned words)
+  // (address & 15) of the first loaded byte of tile row tr, in 32-bit arithmetic: (base + ys * rowbytes) mod 16
+  const unsigned ph_base = (unsigned)((reinterpret_cast<uintptr_t>(img) + (unsigned)c0 - 8u) & 15u);
+  const unsigned rb16 = (unsigned)s.rowbytes & 15u;
+  auto row_ph16 = [&](int tr) { return (ph_base + ((unsigned)row_y(tr) & 15u) * rb16) & 15u; };
+  // Tile byte t of row tr (t = -8 .. TWB + 3) sits at shared offset tr * SROW + 8 + ph16 + t: the readers below
+  // split ph16 into a word offset (ph16 & 12, folded into their addresses) and a byte phase (ph16 & 3, a funnel shift).
+  // A WARP owns a tile row (rows warp, warp + 8, ...): the aligned 16-byte chunks that cover it go to shared memory
+  // with cp.async - every row of the tile in flight at once, nothing waits in registers.  (Round 1 copied 4-byte
+  // words: ~300 LDGSTS per tile at ~8 LSU cycles each, as long as the tile's whole HBM time.)
+  constexpr int N16 = FA_TWB / 16 + 2;              // chunks per tile row: 15 + TWB + 12 bytes at most
   const int warp = tid >> 5, lane = tid & 31;
-  const int nwl = min(NW, ((s.rowbytes - c0 + 11) >> 2) + 1);   // words that hold bytes of the row
+  const int span = min(FA_TWB + 12, s.rowbytes - c0 + 12);     // bytes from c0 - 8 that hold row data (+ slack)
 #pragma unroll 1
   for (int tr = warp; tr < rows; tr += FA_THREADS / 32) {
-    const uint8_t* src = row_src(tr);
-    const uint8_t* base = src - (reinterpret_cast<uintptr_t>(src) & 3u);
-    uint32_t* sdst = reinterpret_cast<uint32_t*>(smem + tr * FA_SROW + FA_APRON - 8);
-    if (base >= img && base + 4 * NW <= img_end) {
+    const uint8_t* src = img + (int64_t)row_y(tr) * s.rowbytes + c0 - 8;
+    const unsigned ph = (unsigned)(reinterpret_cast<uintptr_t>(src) & 15u);
+    const uint8_t* base = src - ph;
+    const int n16 = min(N16, (int)(ph + (unsigned)span + 15u) >> 4);
+    uint8_t* sdst = smem + tr * FA_SROW;
+    if (base >= img && base + 16 * n16 <= img_end) {
       const uint32_t sa = (uint32_t)__cvta_generic_to_shared(sdst);
 #pragma unroll
-      for (int i = 0; i < (NW + 31) / 32; ++i) {
+      for (int i = 0; i < (N16 + 31) / 32; ++i) {
         const int j = lane + 32 * i;
-        if (j < nwl)
-          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa + 4 * j), "l"(base + 4 * j) : "memory");
+        if (j < n16)
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa + 16 * j), "l"(base + 16 * j) : "memory");
       }
-    } else {                                        // first / last rows of an image: bytes outside it read as 0
-      for (int j = lane; j < nwl; j += 32) sdst[j] = guarded_word(base + 4 * j, img, img_end);
+    } else {                                        // first / last rows of a batch: bytes outside it read as 0
+      uint32_t* sw = reinterpret_cast<uint32_t*>(sdst);
+      for (int j = lane; j < 4 * n16; j += 32) sw[j] = guarded_word(base + 4 * j, img, img_end);
     }
   }
   asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
@@ -107,7 +113,7 @@ __global__ void __launch_bounds__(FA_THREADS, 3) k_filter3_tile_any(ImageSet s) 
   const bool right_edge = (s.rowbytes <= c0 + FA_TWB + 3);
   if (left_edge || right_edge) {
     if (tid < rows) {
-      uint8_t* srow = smem + tid * FA_SROW + FA_APRON - c0 + row_phase(tid);
+      uint8_t* srow = smem + tid * FA_SROW + 8 + row_ph16(tid) - c0;
       if (left_edge) {
         const int sp3 = 3 * border_map(-1, s.w, F::BORDER);
 #pragma unroll
@@ -129,21 +135,14 @@ __global__ void __launch_bounds__(FA_THREADS, 3) k_filter3_tile_any(ImageSet s) 
     const int o0 = band * BAND_H;
     const int nrows = min(BAND_H, s.h - y0 - o0);
     if (c < s.rowbytes && nrows > 0) {
-      const uint8_t* sp = smem + FA_APRON + 4 * KW * q + o0 * FA_SROW;
+      const uint8_t* sp = smem + 8 + 4 * KW * q + o0 * FA_SROW;
       auto load_row = [&](int tr, typename F::Part& p) {
-        const uint8_t* rp = sp + tr * FA_SROW;
-        const unsigned sh = 8u * row_phase(o0 + tr);
-        uint32_t R[KW + 3];                             // raw aligned words; tile byte t sits `phase` bytes further
-        R[0] = *reinterpret_cast<const uint32_t*>(rp - 4);
-        if (KW == 4) {
-          const uint4 v = *reinterpret_cast<const uint4*>(rp);
-          R[1] = v.x; R[2] = v.y; R[3] = v.z; R[4] = v.w;
-        } else {
-          const uint2 v = *reinterpret_cast<const uint2*>(rp);
-          R[1] = v.x; R[2] = v.y;
-        }
-        const uint2 t = *reinterpret_cast<const uint2*>(rp + 4 * KW);
-        R[KW + 1] = t.x; R[KW + 2] = t.y;
+        const unsigned ph = row_ph16(o0 + tr);
+        const uint32_t* rp = reinterpret_cast<const uint32_t*>(sp + tr * FA_SROW + (ph & 12u));   // word offset of the row
+        const unsigned sh = 8u * (ph & 3u);
+        uint32_t R[KW + 3];                             // raw aligned words; tile byte t sits (ph & 3) bytes further
+#pragma unroll
+        for (int i = 0; i < KW + 3; ++i) R[i] = rp[i - 1];   // (the word offset rules out vector loads)
         uint32_t w[KW + 2];
 #pragma unroll
         for (int i = 0; i < KW + 2; ++i) w[i] = __funnelshift_r(R[i], R[i + 1], sh);   // (shift 0 returns R[i])
@@ -205,22 +204,32 @@ __global__ void __launch_bounds__(FA_THREADS, 3) k_filter3_tile_any(ImageSet s) 
   }
 }
 
-template <int FILTER>
-static cudaError_t launch_tile_any(const ImageSet& s, cudaStream_t st) {
+template <int FILTER, int TWB>
+static cudaError_t launch_tile_any_w(const ImageSet& s, cudaStream_t st) {
   constexpr int KW = FILTER == FK_MEDIAN3 ? 2 : 4;
   static bool attr_done[64] = {};               // per device: the attribute lives in the context
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (!attr_done[dev & 63]) {
-    const cudaError_t e = cudaFuncSetAttribute(k_filter3_tile_any<FILTER, KW>,
-                                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FA_SMEM);
+  const int dev = current_device() & 63;
+  if (!attr_done[dev]) {
+    const cudaError_t e = cudaFuncSetAttribute(k_filter3_tile_any<FILTER, KW, TWB>,
+                                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FaGeom<TWB>::SMEM);
     if (e != cudaSuccess) return e;
-    attr_done[dev & 63] = true;
+    attr_done[dev] = true;
   }
-  const dim3 grid((s.rowbytes + FA_TWB - 1) / FA_TWB, (s.h + FA_TH - 1) / FA_TH, s.count);
-  k_filter3_tile_any<FILTER, KW><<<grid, FA_THREADS, FA_SMEM, st>>>(s);
+  const dim3 grid((s.rowbytes + TWB - 1) / TWB, (s.h + FaGeom<TWB>::TH - 1) / FaGeom<TWB>::TH, s.count);
+  k_filter3_tile_any<FILTER, KW, TWB><<<grid, FA_THREADS, FaGeom<TWB>::SMEM, st>>>(s);
   count_launch();
   return cudaGetLastError();
+}
+
+template <int FILTER>
+static cudaError_t launch_tile_any(const ImageSet& s, cudaStream_t st) {
+  auto padded = [&](int twb) { return (s.rowbytes + twb - 1) / twb * twb; };
+  int best = 1024;                              // least padding; ties go to the wider tile (fewer apron words)
+  if (padded(512) < padded(best)) best = 512;
+  if (padded(256) < padded(best)) best = 256;
+  if (best == 1024) return launch_tile_any_w<FILTER, 1024>(s, st);
+  if (best == 512) return launch_tile_any_w<FILTER, 512>(s, st);
+  return launch_tile_any_w<FILTER, 256>(s, st);
 }
 
 cudaError_t launch_filter3_any(int filter, const ImageSet& s, cudaStream_t st) {
