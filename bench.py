@@ -490,6 +490,18 @@ def run_b200(args):
         filt[fs] = {"ms": round(fms, 4), "hbm_frac": round(mpix_batch * 1e6 * ALGO_BYTES_PER_PIXEL / (fms * 1e-3) / 1e9 / peak_gbs, 3)}
     del plans
     api._PLANS.clear()
+    # the same filters on the other row alignments: 1080p (rows too wide for the marching kernel), VOC landscape
+    # 375 x 500 (rows of 4 mod 8 bytes), VOC portrait 500 x 375 and 333 x 499 (W % 4 != 0: re-aligning tile kernel)
+    shapes = {}
+    for n_s, h_s, w_s in ((128, 1080, 1920), (1024, 375, 500), (1024, 500, 375), (1024, 333, 499)):
+        b_s = smooth_batch_torch(n_s, h_s, w_s, dev, 77)
+        o_s = torch.empty_like(b_s)
+        mp = n_s * h_s * w_s / 1e6
+        shapes["%dx%dx%d" % (n_s, h_s, w_s)] = {
+            fs: round(mp * 1e6 * ALGO_BYTES_PER_PIXEL / (time_plans(cx, [api.Plan(n_s, h_s, w_s, fs, local)], b_s, o_s, 0, 10) * 1e-3)
+                      / 1e9 / peak_gbs, 3) for fs in ("original_gaus_blur", "original_mean", "original_median")}
+        del b_s, o_s
+    api._PLANS.clear()
 
     # ---- all five BASELINE configs at full size; strong scaling of C3 / C5 under --gpus N --------------------
     del batch, out
@@ -558,7 +570,9 @@ def run_b200(args):
                     "ceiling": "plain pinned H2D + D2H of one spec's bytes at the same time on two streams, no kernels, "
                                "every rank at once (max over ranks), measured in this run"},
             "roofline": roofline, "cpu_baseline": cpu,
-            "detail": {"per_spec": per_spec, "filter_only": filt, "checksum_xor": checksum},
+            "detail": {"per_spec": per_spec, "filter_only": filt,
+                       "filter_only_shapes": {"unit": "fraction of the measured HBM peak at 6 B/pixel", **shapes},
+                       "checksum_xor": checksum},
             "psnr": {"unit": "dB vs the clean batch, mean over all images of all ranks",
                      "gathered": "per-image (checksum u64, sse f64) all_gather over NCCL" if world > 1 else "one rank",
                      **psnr},

@@ -30,6 +30,7 @@ struct RunCtx {
   const b2d_fields* fields;
   uint64_t seed, first_global;
   cudaStream_t st;
+  bool defer_denoise = false;   // run_range: every group stages its noised uint8 image, ONE denoise launch follows
 };
 
 ImageSet make_set(const b2d_plan* p, const uint8_t* in, uint8_t* out, const SpecGroup& g, int lo, int hi) {
@@ -63,6 +64,17 @@ int denoise_u8(const RunCtx& c, const b2d_spec& sp, const ImageSet& s) {
     return B2D_OK;
   }
   return run_denoise_pass(*c.p, sp, s, c.ws, c.st);
+}
+
+// Mixed batches whose groups all end in the same stand-alone uint8 denoiser (median 5 / 7, bilateral): the denoiser is
+// launched once over the whole range instead of once per group (BASELINE config C5: 10 groups -> median 7 x 7; at
+// 512 images per GPU the per-group launches are small and their tails add up).
+bool same_denoiser(const b2d_spec& a, const b2d_spec& b) {
+  return a.denoise == b.denoise && a.ksize == b.ksize && a.d == b.d && a.sigma_color == b.sigma_color &&
+         a.sigma_space == b.sigma_space;
+}
+bool standalone_u8_denoiser(const b2d_spec& sp) {
+  return (sp.denoise == B2D_DENOISE_MEDIAN && sp.ksize != 3) || sp.denoise == B2D_DENOISE_BILATERAL;
 }
 
 int run_group(const RunCtx& c, const SpecGroup& g, int lo, int hi) {
@@ -108,7 +120,7 @@ int run_group(const RunCtx& c, const SpecGroup& g, int lo, int hi) {
       ImageSet ps = s;
       ps.out = dst;
       CK(launch_poisson(ps, na, p->d_poisson, c.st));
-      if (sp.denoise == B2D_DENOISE_NONE) return B2D_OK;
+      if (sp.denoise == B2D_DENOISE_NONE || c.defer_denoise) return B2D_OK;
       ImageSet ds = s;
       ds.in = stage;
       if (sp.denoise == B2D_DENOISE_WAVELET) {
@@ -148,7 +160,7 @@ int run_group(const RunCtx& c, const SpecGroup& g, int lo, int hi) {
                          ? run_quant(*p, sp, ps, tables, c.fields, c.seed, c.first_global, c.st)
                          : run_bloom(*p, ps, g, lo, hi, tables, c.fields, c.seed, c.first_global, c.st);
       if (rc) return rc;
-      if (sp.denoise == B2D_DENOISE_NONE) return B2D_OK;
+      if (sp.denoise == B2D_DENOISE_NONE || c.defer_denoise) return B2D_OK;
       ImageSet ds = s;
       ds.in = stage;
       if (sp.denoise == B2D_DENOISE_WAVELET) {           // quant_wavelet: denoise_wavelet(uint8 palette image), minibatch.py:501-537
@@ -174,23 +186,43 @@ int run_group(const RunCtx& c, const SpecGroup& g, int lo, int hi) {
     CK(launch_fused3(kind, f3, s, na, c.st));          // the one-pass hot path
     return B2D_OK;
   }
-  if (kind == NK_NONE) return denoise_u8(c, sp, s);    // `original_*`: nothing to stage, the denoiser reads the input
+  if (kind == NK_NONE && !c.defer_denoise) return denoise_u8(c, sp, s);    // `original_*`: nothing to stage, the denoiser reads the input
   // two-pass: noise -> stage (uint8) -> denoiser
   ImageSet ns = s;
   ns.out = stage;
   CK(launch_noise_only(kind, mode, ns, na, c.st));
+  if (c.defer_denoise) return B2D_OK;
   ImageSet ds = s;
   ds.in = stage;
   return denoise_u8(c, sp, ds);
 }
 
-int run_range(const RunCtx& c, int img0, int cnt) {
+int run_range(const RunCtx& c0, int img0, int cnt) {
+  RunCtx c = c0;
+  // groups that have images in [img0, img0 + cnt)
+  const SpecGroup* first = nullptr;
+  int live = 0;
+  bool same = true;
+  for (const SpecGroup& g : c.p->groups) {
+    const auto lo = std::lower_bound(g.images.begin(), g.images.end(), img0);
+    if (lo == g.images.end() || *lo >= img0 + cnt) continue;
+    ++live;
+    if (!first) first = &g;
+    else same = same && same_denoiser(first->spec, g.spec);
+  }
+  c.defer_denoise = live > 1 && same && standalone_u8_denoiser(first->spec);
   for (const SpecGroup& g : c.p->groups) {
     const int lo = (int)(std::lower_bound(g.images.begin(), g.images.end(), img0) - g.images.begin());
     const int hi = (int)(std::lower_bound(g.images.begin(), g.images.end(), img0 + cnt) - g.images.begin());
     if (hi <= lo) continue;
     const int rc = run_group(c, g, lo, hi);
     if (rc) return rc;
+  }
+  if (c.defer_denoise) {                              // every image of the range now sits noised in the staging set
+    ImageSet s;
+    s.in = c.ws + c.p->off_stage; s.out = c.out; s.h = c.p->h; s.w = c.p->w; s.rowbytes = c.p->rowbytes; s.elems = c.p->elems;
+    s.count = cnt; s.first = img0; s.list = nullptr;
+    return denoise_u8(c, first->spec, s);
   }
   return B2D_OK;
 }

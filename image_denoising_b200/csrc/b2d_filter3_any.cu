@@ -24,7 +24,6 @@
 namespace b2d {
 
 constexpr int FA_THREADS = 256;
-constexpr int FA_XW = 3;                   // words per row past the tile's own: [c0 - 8, c0 + TWB + 4) is loaded
 // Tile geometry: TWB bytes x (32 KiB / TWB) rows - 1024 x 32, 512 x 64 or 256 x 128.  Same shared memory, same 8-row
 // (median: 16-row) bands for all three; the launcher takes the width that pads a row least: 1125-byte rows (W = 375, the
 // reference's portrait VOC images) fill 5 tiles of 256 to 88 %, but 2 tiles of 1024 only to 55 %.
