@@ -23,12 +23,15 @@ therefore pinned as follows:
   * ``Automold.add_sun_flare`` is imported from /root/reference at fixture
     generation time (tests/golden/make_golden.py) and the outputs committed;
   * the skimage / pywt restatement is "parity unpinned" against the real
-    libraries (they cannot be installed: no network); it is held by property
-    tests (perfect reconstruction, Parseval, BT.601 anchors, hand-computed Haar
-    cases) in tests/test_oracle_wavelet.py;
+    libraries (they cannot be installed: no network); it is held by
+    tests/test_oracle_wavelet.py: property tests (perfect reconstruction,
+    Parseval, BT.601 anchors, hand-computed Haar cases), a second, independently
+    derived transform (dense analysis / synthesis matrices from the filter
+    definitions and the symmetric-extension rule) the oracle must equal on odd
+    and even sizes, and the known answers printed in the PyWavelets docs;
   * ``oracle/jpeg.py`` (the ``cv2.imread`` stage in front of the path) restates libjpeg's
     baseline decoder and IS pinned: byte-identical to ``cv2.imdecode`` in tests/test_oracle_jpeg.py;
   * ``oracle/nms.py`` (SURVEY 8(f) f4) is pinned by golden vectors of the reference's lib/nms/py_cpu_nms.py;
-  * tests/golden/manifest.json pins 267 oracle results by SHA-256 (tests/test_golden_cpu.py).
+  * tests/golden/manifest.json pins 525 oracle results (the whole noise x denoise x level ladder) by SHA-256 (tests/test_golden_cpu.py).
 """
 from . import noise, denoise, wavelet, closures, jpeg, nms  # noqa: F401

@@ -11,7 +11,10 @@ The algorithm below restates their published source:
   pywt/_multilevel.py              (wavedecn, waverecn), pywt/_thresholding.py
 and is anchored on the reference's call sites (minibatch.py:92-96 - bior1.5,
 automatic levels; test.py_bkp:1913-1916 - db1, wavelet_levels=3).  It is held
-by the property tests in tests/test_oracle_wavelet.py.
+by tests/test_oracle_wavelet.py: property tests, an independent dense-matrix
+transform it must equal, and the known answers of the PyWavelets documentation.
+`sigma_census` / the `sigmas=` argument exist for the stage-wise GPU parity check
+(tests/wavelet_check.py); the reference's own behaviour is `denoise_wavelet(x, ...)`.
 """
 import numpy as np
 
