@@ -200,8 +200,12 @@ extern "C" int b2d_stats(b2d_plan* plan, const uint8_t* d_ref, const uint8_t* d_
   if (d_sse) CK(cudaMemsetAsync(d_sse, 0, sizeof(double) * plan->n, st));
   unsigned bx = (unsigned)std::min<uint64_t>(64, (plan->elems + 256 * 16 - 1) / (256 * 16));
   if (bx < 1) bx = 1;
-  k_stats<<<dim3(bx, plan->n), 256, 0, st>>>(d_ref, d_out, plan->elems,
-                                              reinterpret_cast<unsigned long long*>(d_checksum), d_sse);
+  for (int a = 0; a < plan->n; a += 65535) {          // the image index is grid.y
+    const int cnt = std::min(65535, plan->n - a);
+    const size_t off = (size_t)a * plan->elems;
+    k_stats<<<dim3(bx, cnt), 256, 0, st>>>(d_ref ? d_ref + off : nullptr, d_out + off, plan->elems,
+                                           reinterpret_cast<unsigned long long*>(d_checksum) + a, d_sse ? d_sse + a : nullptr);
+  }
   count_launch();
   CK(cudaGetLastError());
   return B2D_OK;

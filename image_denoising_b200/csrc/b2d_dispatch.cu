@@ -211,18 +211,24 @@ int run_range(const RunCtx& c0, int img0, int cnt) {
     else same = same && same_denoiser(first->spec, g.spec);
   }
   c.defer_denoise = live > 1 && same && standalone_u8_denoiser(first->spec);
+  // the image index is a grid dimension (<= 65535) in every kernel: larger groups go out in several launches
+  constexpr int kMaxLaunchImages = 65535;
   for (const SpecGroup& g : c.p->groups) {
     const int lo = (int)(std::lower_bound(g.images.begin(), g.images.end(), img0) - g.images.begin());
     const int hi = (int)(std::lower_bound(g.images.begin(), g.images.end(), img0 + cnt) - g.images.begin());
-    if (hi <= lo) continue;
-    const int rc = run_group(c, g, lo, hi);
-    if (rc) return rc;
+    for (int a = lo; a < hi; a += kMaxLaunchImages) {
+      const int rc = run_group(c, g, a, std::min(hi, a + kMaxLaunchImages));
+      if (rc) return rc;
+    }
   }
   if (c.defer_denoise) {                              // every image of the range now sits noised in the staging set
-    ImageSet s;
-    s.in = c.ws + c.p->off_stage; s.out = c.out; s.h = c.p->h; s.w = c.p->w; s.rowbytes = c.p->rowbytes; s.elems = c.p->elems;
-    s.count = cnt; s.first = img0; s.list = nullptr;
-    return denoise_u8(c, first->spec, s);
+    for (int a = 0; a < cnt; a += kMaxLaunchImages) {
+      ImageSet s;
+      s.in = c.ws + c.p->off_stage; s.out = c.out; s.h = c.p->h; s.w = c.p->w; s.rowbytes = c.p->rowbytes; s.elems = c.p->elems;
+      s.count = std::min(kMaxLaunchImages, cnt - a); s.first = img0 + a; s.list = nullptr;
+      const int rc = denoise_u8(c, first->spec, s);
+      if (rc) return rc;
+    }
   }
   return B2D_OK;
 }

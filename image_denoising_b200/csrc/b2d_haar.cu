@@ -495,7 +495,7 @@ int run_haar(const b2d_plan& p, const ImageSet& s, int kind, const NoiseArgs& na
   hg.w2 = p.w / 2;
   hg.dd_floats = (size_t)(p.h / 2) * (p.w / 2);
   const size_t per_img = 3 * (hg.dd_floats * sizeof(float) + sizeof(WvStats) + 2 * WV_BINS * sizeof(unsigned int));
-  const int chunk = (int)std::min<size_t>((size_t)s.count, (avail - 1024) / per_img);
+  const int chunk = (int)std::min<size_t>(std::min<size_t>((size_t)s.count, 21845), (avail - 1024) / per_img);   // 3 planes per image in grid.z
   if (chunk < 1) return fail(B2D_ERR_INVALID, "wavelet: workspace too small for the Haar path");
   float* dd1 = reinterpret_cast<float*>(wbase);
   WvStats* stats = reinterpret_cast<WvStats*>(wbase + (size_t)chunk * 3 * hg.dd_floats * sizeof(float));

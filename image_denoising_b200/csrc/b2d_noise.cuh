@@ -84,14 +84,24 @@ __device__ __forceinline__ float magic_hi16(uint32_t w) { return __uint_as_float
 template <int I>
 __device__ __forceinline__ float magic_byte(uint32_t w) { return __uint_as_float(prmt(w, B2D_MAGIC, 0x7440u | I)); }
 
-__device__ __forceinline__ void normal_pair(uint32_t r32, float sigma, float& n0, float& n1) {
+// Box-Muller in polar form: radius sigma * sqrt(-2 ln u1) and (cos, sin) of theta, from one 32-bit Philox word.
+// theta comes from the magic float 2^23 + kb in ONE FFMA: its constant carries -2^23 * c1 (the product is exact inside the
+// FFMA, so the cancellation costs nothing; the angle grid is shifted by < 3e-5 rad, a constant).
+__device__ __forceinline__ void normal_polar(uint32_t r32, float sigma, float& rad, float& c, float& s) {
   const float a = magic_lo16(r32) - 8388607.5f;                       // ka + 0.5, exact
-  const float kb = magic_hi16(r32) - 8388608.0f;                      // exact
   const float s2 = sigma * sigma * 1.3862943611198906f;               // sigma^2 * 2 ln 2 (loop invariant)
-  const float rad = fast_sqrt(fmaf(fast_lg2(a), -s2, 16.0f * s2));    // sigma * sqrt(-2 ln u1)
-  const float th = fmaf(kb, 6.283185307179586f / 65536.0f, 3.141592653589793f / 65536.0f);
-  n0 = rad * fast_cos(th);
-  n1 = rad * fast_sin(th);
+  rad = fast_sqrt(fmaf(fast_lg2(a), -s2, 16.0f * s2));                // sigma * sqrt(-2 ln u1)
+  constexpr float c1 = 6.283185307179586f / 65536.0f;
+  constexpr float c0 = (float)(3.141592653589793 / 65536.0 - 8388608.0 * (double)c1);
+  const float th = fmaf(magic_hi16(r32), c1, c0);                     // 2 pi (kb + 0.5) / 65536
+  c = fast_cos(th);
+  s = fast_sin(th);
+}
+__device__ __forceinline__ void normal_pair(uint32_t r32, float sigma, float& n0, float& n1) {
+  float rad, c, s;
+  normal_polar(r32, sigma, rad, c, s);
+  n0 = rad * c;
+  n1 = rad * s;
 }
 
 template <int MODE, bool SPECKLE>
@@ -115,17 +125,19 @@ struct NormalNoise {
     const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      float n0, n1;
-      normal_pair(rw[j], a.p0, n0, n1);
+      // gaussian: x = v + 255 n = cos * (255 rad) + v in ONE fma (the radius is drawn at sigma * 255), speckle: v + v n.
+      // Exact value, one rounding toward zero - the packed operator below truncates the same exact value, so both
+      // agree on the uint8 result.
+      float rad, cs, sn;
+      normal_polar(rw[j], SPECKLE ? a.p0 : a.p0 * 255.0f, rad, cs, sn);
+      const float n0 = SPECKLE ? rad * cs : rad * cs * (1.0f / 255.0f), n1 = SPECKLE ? rad * sn : rad * sn * (1.0f / 255.0f);
       if (MODE == NM_DUMP) {
         if (in_image(a, g, 2 * j)) a.dump0[field_index(a, g, 2 * j)] = n0;
         if (in_image(a, g, 2 * j + 1)) a.dump0[field_index(a, g, 2 * j + 1)] = n1;
       }
-      // exact v + 255 n (or v + v n), one rounding toward zero; the packed operator below
-      // truncates the same exact value, so both agree on the uint8 result
       const float v0 = (float)v[2 * j], v1 = (float)v[2 * j + 1];
-      const float x0 = SPECKLE ? __fmaf_rz(v0, n0, v0) : __fmaf_rz(n0, 255.0f, v0);
-      const float x1 = SPECKLE ? __fmaf_rz(v1, n1, v1) : __fmaf_rz(n1, 255.0f, v1);
+      const float x0 = SPECKLE ? __fmaf_rz(v0, n0, v0) : __fmaf_rz(cs, rad, v0);
+      const float x1 = SPECKLE ? __fmaf_rz(v1, n1, v1) : __fmaf_rz(sn, rad, v1);
       const float c0 = fminf(fmaxf(x0, 0.0f), 255.0f), c1 = fminf(fmaxf(x1, 0.0f), 255.0f);
       if (xf) { xf[2 * j] = c0; xf[2 * j + 1] = c1; }
       v[2 * j] = (uint32_t)__float2int_rz(c0);
@@ -526,10 +538,11 @@ struct PackedNoise<NK_SAP> {
 template <bool SPECKLE>
 struct PackedNormal {
   static constexpr bool kNative = true;
+  // gaussian: trig = cos / sin, rad = 255 sigma sqrt(-2 ln u): x = trig * rad + v; speckle: trig * rad = n, x = v n + v
   template <int I>
-  static __device__ __forceinline__ uint32_t elem(uint32_t w, float n) {
+  static __device__ __forceinline__ uint32_t elem(uint32_t w, float trig, float rad) {
     const float mv = magic_byte<I>(w);
-    const float t = SPECKLE ? __fmaf_rz(mv - 8388608.0f, n, mv) : __fmaf_rz(n, 255.0f, mv);
+    const float t = SPECKLE ? __fmaf_rz(mv - 8388608.0f, rad * trig, mv) : __fmaf_rz(trig, rad, mv);
     return __float_as_uint(t);
   }
   static __device__ __forceinline__ uint32_t clamp2(uint32_t t0, uint32_t t1) {
@@ -537,15 +550,16 @@ struct PackedNormal {
   }
   static __device__ __forceinline__ uint2 apply(const NoiseArgs& a, const GroupCtx& g, uint2 w) {
     const uint4 r = group_random(a, g, 0);
-    float n0, n1, n2, n3, n4, n5, n6, n7;
-    normal_pair(r.x, a.p0, n0, n1);
-    normal_pair(r.y, a.p0, n2, n3);
-    normal_pair(r.z, a.p0, n4, n5);
-    normal_pair(r.w, a.p0, n6, n7);
-    const uint32_t l01 = clamp2(elem<0>(w.x, n0), elem<1>(w.x, n1));
-    const uint32_t l23 = clamp2(elem<2>(w.x, n2), elem<3>(w.x, n3));
-    const uint32_t l45 = clamp2(elem<0>(w.y, n4), elem<1>(w.y, n5));
-    const uint32_t l67 = clamp2(elem<2>(w.y, n6), elem<3>(w.y, n7));
+    const float sg = SPECKLE ? a.p0 : a.p0 * 255.0f;
+    float r0, r1, r2, r3, n0, n1, n2, n3, n4, n5, n6, n7;               // n = (cos, sin) per Philox word
+    normal_polar(r.x, sg, r0, n0, n1);
+    normal_polar(r.y, sg, r1, n2, n3);
+    normal_polar(r.z, sg, r2, n4, n5);
+    normal_polar(r.w, sg, r3, n6, n7);
+    const uint32_t l01 = clamp2(elem<0>(w.x, n0, r0), elem<1>(w.x, n1, r0));
+    const uint32_t l23 = clamp2(elem<2>(w.x, n2, r1), elem<3>(w.x, n3, r1));
+    const uint32_t l45 = clamp2(elem<0>(w.y, n4, r2), elem<1>(w.y, n5, r2));
+    const uint32_t l67 = clamp2(elem<2>(w.y, n6, r3), elem<3>(w.y, n7, r3));
     return make_uint2(prmt(l01, l23, 0x6420u), prmt(l45, l67, 0x6420u));
   }
 };

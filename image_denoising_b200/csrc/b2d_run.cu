@@ -56,7 +56,7 @@ extern "C" int b2d_plan_create(b2d_plan** out, int device, int n, int h, int w, 
   if (!out || !specs) return fail(B2D_ERR_INVALID, "b2d_plan_create: null argument");
   *out = nullptr;
   if (n < 0 || h <= 0 || w <= 0) return fail(B2D_ERR_INVALID, "b2d_plan_create: bad shape n=%d h=%d w=%d", n, h, w);
-  if (n > 65535) return fail(B2D_ERR_INVALID, "b2d_plan_create: at most 65535 images per plan (the image index is a grid dimension); split the batch");
+  if (n > (1 << 24)) return fail(B2D_ERR_INVALID, "b2d_plan_create: at most 2^24 images per plan");
   if (n_specs != 1 && n_specs != n) return fail(B2D_ERR_INVALID, "n_specs must be 1 or n (got %d, n=%d)", n_specs, n);
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)

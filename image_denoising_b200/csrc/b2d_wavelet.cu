@@ -848,7 +848,8 @@ constexpr size_t WV_BUDGET = 6ull << 30;           // workspace cap: images are 
 
 static int wv_chunk(const WvGeom& g, int n) {
   const size_t per_img = 3 * g.chan_floats * sizeof(float);
-  return (int)std::max<size_t>(1, std::min<size_t>((size_t)n, WV_BUDGET / std::max<size_t>(per_img, 1)));
+  // (3 planes per image index grid.z: at most 21845 images per chunk)
+  return (int)std::max<size_t>(1, std::min<size_t>(std::min<size_t>((size_t)n, 21845), WV_BUDGET / std::max<size_t>(per_img, 1)));
 }
 
 size_t wavelet_workspace_bytes(const b2d_plan& p) {

@@ -137,8 +137,8 @@ int b2d_parse_spec(const char* spec, b2d_spec* out);
 
 /* A plan fixes (device, N, H, W) and one spec per image (n_specs == N) or one
  * spec for the whole batch (n_specs == 1).  Replaces the per-image closure
- * definition + dispatch of test.py:189-1784.  N <= 65535 (larger batches: several
- * plans / calls with first_global_image_index advanced, results are identical). */
+ * definition + dispatch of test.py:189-1784.  N <= 2^24 (groups of more than 65535 images go out in
+ * several launches internally: the image index is a grid dimension). */
 int b2d_plan_create(b2d_plan** out, int device, int n, int h, int w,
                     const b2d_spec* specs, int n_specs);
 int b2d_plan_workspace_bytes(const b2d_plan* plan, size_t* bytes);

@@ -100,3 +100,28 @@ def test_tiny_wavelet(cuda, shape, wl):
         want = C.apply_denoise(batch[i], "wavelet", wavelet=wl[0], wavelet_levels=wl[1] or None)
         d = np.abs(got[i].astype(int) - want.astype(int))
         assert d.max() <= 1, (shape, wl, i, int(d.max()))
+
+
+def test_more_images_than_a_grid_dimension(cuda):
+    """70 000 tiny images in one plan: the image index is a grid dimension (<= 65535) in every kernel, so the
+    dispatcher, b2d_stats and the wavelet chunking split the launches; results must equal per-slice runs."""
+    from image_denoising_b200 import api
+    n, h, w = 70000, 8, 8
+    rng = np.random.RandomState(4)
+    batch = torch.from_numpy(rng.randint(0, 256, (n, h, w, 3)).astype(np.uint8)).to(cuda)
+    for spec, kw in (("sap_mean_var0.4", {}), ("gaussian_median_var1.0", {"ksize": 5}), ("poisson_median", {}),
+                     ("gaussian_wavelet_var1.0", {"wavelet": "db1", "levels": 3})):
+        plan = api.get_plan(n, h, w, spec, cuda.index, **kw)
+        full = plan.run(batch, seed=9, first_index=0)
+        for lo in (0, 65530, 69990):
+            part = api.apply(batch[lo:lo + 10].contiguous(), spec, seed=9, first_index=lo, **kw)
+            assert torch.equal(part, full[lo:lo + 10]), (spec, lo)
+        cs, sse = plan.stats(full, batch)
+        cs2, sse2 = api.get_plan(10, h, w, spec, cuda.index, **kw).stats(full[69990:].contiguous(), batch[69990:].contiguous())
+        assert torch.equal(cs[69990:], cs2) and torch.equal(sse[69990:], sse2), spec
+    # mixed batch with a shared stand-alone denoiser: the single deferred denoise launch is split as well
+    specs = ["poisson_median" if i % 2 else "sap_median_var0.4" for i in range(n)]
+    full = api.get_plan(n, h, w, specs, cuda.index, ksize=5).run(batch, seed=9)
+    for lo in (0, 65534, 69990):
+        part = api.apply(batch[lo:lo + 10].contiguous(), specs[lo:lo + 10], seed=9, first_index=lo, ksize=5)
+        assert torch.equal(part, full[lo:lo + 10]), lo
