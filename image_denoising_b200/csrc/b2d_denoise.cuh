@@ -19,8 +19,10 @@ cudaError_t launch_filter3_any(int filter, const ImageSet& s, cudaStream_t st);
 }  // namespace b2d
 
 namespace b2d {
-// median 5/7, bilateral (uint8 in -> uint8 out, already noised)
-int run_denoise_pass(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, uint8_t* ws, cudaStream_t st);
+// median 5/7, bilateral (uint8 in -> uint8 out).  noisy_input: the image comes out of a noise pass (bilateral then clamps
+// its colour-LUT index at the first all-zero entry: same bits, no shared-memory conflicts on the zero-weight taps)
+int run_denoise_pass(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, uint8_t* ws, cudaStream_t st,
+                     bool noisy_input = true);
 // quant / bloom: pixel-granular corruption written as a uint8 image (s.out); `tables` = plan scratch
 size_t quant_table_bytes(int n);
 size_t bloom_table_bytes(int n, int h);

@@ -54,7 +54,7 @@ int filter3_kind(const b2d_spec& sp) {
 }
 
 // denoise a uint8 image set that is already noised (src -> dst)
-int denoise_u8(const RunCtx& c, const b2d_spec& sp, const ImageSet& s) {
+int denoise_u8(const RunCtx& c, const b2d_spec& sp, const ImageSet& s, bool noisy_input = true) {
   const int f3 = filter3_kind(sp);
   if (f3 != FK_NONE) {
     NoiseArgs none{};
@@ -63,7 +63,7 @@ int denoise_u8(const RunCtx& c, const b2d_spec& sp, const ImageSet& s) {
     else CK(launch_filter3_any(f3, s, c.st));
     return B2D_OK;
   }
-  return run_denoise_pass(*c.p, sp, s, c.ws, c.st);
+  return run_denoise_pass(*c.p, sp, s, c.ws, c.st, noisy_input);
 }
 
 // Mixed batches whose groups all end in the same stand-alone uint8 denoiser (median 5 / 7, bilateral): the denoiser is
@@ -186,7 +186,7 @@ int run_group(const RunCtx& c, const SpecGroup& g, int lo, int hi) {
     CK(launch_fused3(kind, f3, s, na, c.st));          // the one-pass hot path
     return B2D_OK;
   }
-  if (kind == NK_NONE && !c.defer_denoise) return denoise_u8(c, sp, s);    // `original_*`: nothing to stage, the denoiser reads the input
+  if (kind == NK_NONE && !c.defer_denoise) return denoise_u8(c, sp, s, false);    // `original_*`: nothing to stage, the denoiser reads the input
   // two-pass: noise -> stage (uint8) -> denoiser
   ImageSet ns = s;
   ns.out = stage;
