@@ -318,7 +318,9 @@ def config_roofline(kind, mpix, ms, per_gpu, peak_gbs, peak_src):
         t = mpix * 1e6 * 539 / (ms * 1e-3) / 1e12 / per_gpu
         return {"bound": "fp32/int issue", "lane_instr_per_pixel": 539, "achieved": t, "peak": LANE_INSTR_PEAK_T,
                 "unit": "T lane-instr/s", "frac": t / LANE_INSTR_PEAK_T,
-                "note": "539 = SURVEY 8(d)'s algorithmic count for d = 9 (49 taps x 11); the kernel executes 467 per pixel"}
+                "note": "539 = SURVEY 8(d)'s algorithmic count for d = 9 (49 taps x 11); the 4 x 2-output kernel executes ~480 "
+                        "per pixel and shares its time between instruction issue (73 %) and shared-memory LUT wavefronts (83 %): "
+                        "profiles/r02l_bilateral.txt"}
     if kind == "latency":
         gbs = mpix * 1e6 * 6.0 / (ms * 1e-3) / 1e9 / per_gpu
         return {"bound": "latency", "achieved": gbs, "peak": peak_gbs, "unit": "GB/s", "frac": gbs / peak_gbs,
