@@ -264,38 +264,62 @@ extern "C" int b2d_run_host(b2d_plan* plan, const uint8_t* h_in, uint8_t* h_out,
     CK(cudaMalloc(&plan->h_d_in, bytes));
     CK(cudaMalloc(&plan->h_d_out, bytes));
     if (plan->ws_bytes) CK(cudaMalloc(&plan->h_d_ws, plan->ws_bytes));
-    for (int i = 0; i < 3; ++i) {
-      CK(cudaStreamCreateWithFlags(&plan->h_streams[i], cudaStreamNonBlocking));
-      CK(cudaEventCreateWithFlags(&plan->h_done[i], cudaEventDisableTiming));
-    }
+    for (int i = 0; i < 3; ++i) CK(cudaStreamCreateWithFlags(&plan->h_streams[i], cudaStreamNonBlocking));
     plan->h_ready = true;
   }
-  // chunks of >= 32 MiB (at least one image) so each copy runs at full PCIe rate (B2D_HOST_CHUNK_MB: diagnostic knob)
+  // chunks of >= 32 MiB (at least one image) so each copy runs at full PCIe rate (B2D_HOST_CHUNK_MB: diagnostic knob;
+  // 32 is the optimum of a 4-128 MiB sweep)
   static const uint64_t chunk_bytes = [] {
     const char* e = knob("B2D_HOST_CHUNK_MB");
     return (uint64_t)(e && atoi(e) > 0 ? atoi(e) : 32) << 20;
   }();
-  const int per = (int)std::max<uint64_t>(1, chunk_bytes / plan->elems);
-  // Chunk k runs H2D -> kernels -> D2H on stream k % 3.  The KERNELS of consecutive chunks are chained with an
-  // event (chunk k + 1 computes after chunk k has computed): every piece of plan scratch that is not indexed by
-  // image - wavelet planes, bilateral / bloom / quant tables, the staging rows a pre-pass reuses - is therefore
-  // used by one chunk at a time, while the copies of the neighbouring chunks still overlap the kernels.  The
-  // kernels of one chunk fill the GPU, so nothing is lost by the chain.
+  static const bool chunk_forced = knob("B2D_HOST_CHUNK_MB") != nullptr;
+  int per = (int)std::max<uint64_t>(1, chunk_bytes / plan->elems);
+  if (!chunk_forced) {
+    // Chunking must not starve the launches: a mixed batch cuts every chunk into its spec groups (keep >= 4 images per
+    // group and chunk), and the per-image pre-passes that are latency bound - k-means fit (quant), fp64 scan (brownian),
+    // the flare tables (bloom) - cost the same for 2 images as for 200, so such plans run in at most 8 chunks.
+    bool latency_bound = false;
+    for (const SpecGroup& g : plan->groups)
+      latency_bound = latency_bound || g.spec.noise == B2D_NOISE_QUANT || g.spec.noise == B2D_NOISE_BROWNIAN ||
+                      g.spec.noise == B2D_NOISE_BLOOM;
+    if (plan->groups.size() > 1) per = std::max(per, 4 * (int)plan->groups.size());
+    if (latency_bound) per = std::max(per, (plan->n + 7) / 8);
+  }
+  per = std::min(per, plan->n);
+  // (ramping the first and last chunks down to per/8 to shorten the one-way fill and drain phases measured no gain)
+  std::vector<int> cut;
+  for (int i = 0; i < plan->n; i += per) cut.push_back(i);
+  cut.push_back(plan->n);
+  const int nchunks = (int)cut.size() - 1;
+  while ((int)plan->h_events.size() < 2 * nchunks) {
+    cudaEvent_t e;
+    CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    plan->h_events.push_back(e);
+  }
+  // Three streams, one per engine: every H2D copy is queued at once on the first (the device buffers hold the whole
+  // batch: nothing is reused, the copies run ahead freely), chunk k computes on the second when its input has landed -
+  // ONE compute stream, so the chunks use the plan's shared scratch (wavelet planes, tables, staging rows) one at a time -
+  // and the third drains chunk k when its kernels are done.
+  cudaStream_t s_in = plan->h_streams[0], s_run = plan->h_streams[1], s_out = plan->h_streams[2];
   int rc = B2D_OK;
   cudaError_t ce = cudaSuccess;
-  int k = 0;
-  for (int img0 = 0; img0 < plan->n && rc == B2D_OK && ce == cudaSuccess; img0 += per, ++k) {
-    const int cnt = std::min(per, plan->n - img0);
-    cudaStream_t st = plan->h_streams[k % 3];
+  for (int k = 0; k < nchunks && ce == cudaSuccess; ++k) {
+    const size_t off = (size_t)cut[k] * plan->elems, len = (size_t)(cut[k + 1] - cut[k]) * plan->elems;
+    ce = cudaMemcpyAsync(plan->h_d_in + off, h_in + off, len, cudaMemcpyHostToDevice, s_in);
+    if (ce == cudaSuccess) ce = cudaEventRecord(plan->h_events[2 * k], s_in);
+  }
+  for (int k = 0; k < nchunks && rc == B2D_OK && ce == cudaSuccess; ++k) {
+    const int img0 = cut[k], cnt = cut[k + 1] - cut[k];
     const size_t off = (size_t)img0 * plan->elems, len = (size_t)cnt * plan->elems;
-    ce = cudaMemcpyAsync(plan->h_d_in + off, h_in + off, len, cudaMemcpyHostToDevice, st);
-    if (ce == cudaSuccess && k > 0) ce = cudaStreamWaitEvent(st, plan->h_done[(k - 1) % 3], 0);
+    ce = cudaStreamWaitEvent(s_run, plan->h_events[2 * k], 0);
     if (ce != cudaSuccess) break;
-    RunCtx c{plan, plan->h_d_in, plan->h_d_out, plan->h_d_ws, nullptr, seed, first_global_image_index, st};
+    RunCtx c{plan, plan->h_d_in, plan->h_d_out, plan->h_d_ws, nullptr, seed, first_global_image_index, s_run};
     rc = run_range(c, img0, cnt);
     if (rc) break;
-    ce = cudaEventRecord(plan->h_done[k % 3], st);
-    if (ce == cudaSuccess) ce = cudaMemcpyAsync(h_out + off, plan->h_d_out + off, len, cudaMemcpyDeviceToHost, st);
+    ce = cudaEventRecord(plan->h_events[2 * k + 1], s_run);
+    if (ce == cudaSuccess) ce = cudaStreamWaitEvent(s_out, plan->h_events[2 * k + 1], 0);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(h_out + off, plan->h_d_out + off, len, cudaMemcpyDeviceToHost, s_out);
   }
   // always drain all three streams: on an error the copies already queued still target the caller's memory
   for (int i = 0; i < 3; ++i) {

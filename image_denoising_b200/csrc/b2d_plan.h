@@ -62,7 +62,7 @@ struct b2d_plan {
   mutable int wv_stats_first, wv_stats_count;   // group-relative index of the chunk's first image, images in it
   // b2d_run_host resources (lazily created)
   uint8_t *h_d_in, *h_d_out, *h_d_ws;
-  cudaStream_t h_streams[3];
-  cudaEvent_t h_done[3];     // "kernels of the chunk on stream i have finished" (chains the compute of consecutive chunks)
+  cudaStream_t h_streams[3]; // copy-in, compute, copy-out
+  std::vector<cudaEvent_t> h_events;   // per chunk: "input landed", "kernels done"
   bool h_ready;
 };

@@ -184,10 +184,8 @@ extern "C" void b2d_plan_destroy(b2d_plan* p) {
   if (p->h_d_out) cudaFree(p->h_d_out);
   if (p->h_d_ws) cudaFree(p->h_d_ws);
   if (p->h_ready)
-    for (int i = 0; i < 3; ++i) {
-      cudaStreamDestroy(p->h_streams[i]);
-      cudaEventDestroy(p->h_done[i]);
-    }
+    for (int i = 0; i < 3; ++i) cudaStreamDestroy(p->h_streams[i]);
+  for (cudaEvent_t e : p->h_events) cudaEventDestroy(e);
   delete p;
 }
 
