@@ -226,6 +226,8 @@ cudaError_t launch_march3(int kind, int filter, const ImageSet& s, const NoiseAr
 bool march3_supported(const ImageSet& s);
 bool march3_a4_supported(const ImageSet& s);
 cudaError_t launch_march3_a4(int filter, const ImageSet& s, const NoiseArgs& na, cudaStream_t st);
+bool strip3_supported(int kind, int filter, const ImageSet& s);
+cudaError_t launch_strip3(int kind, int filter, const ImageSet& s, const NoiseArgs& na, cudaStream_t st);
 
 cudaError_t launch_fused3(int kind, int filter, const ImageSet& s, const NoiseArgs& na, cudaStream_t st) {
   if (s.count <= 0) return cudaSuccess;
@@ -254,6 +256,8 @@ cudaError_t launch_fused3(int kind, int filter, const ImageSet& s, const NoiseAr
   // (0.32 / 0.35 ms vs 0.48 / 0.50 ms: no apron rows, register prefetch); with a generator in the
   // prologue the tiles win (0.69 vs 0.78 ms for sap_mean: longer phases, fewer barriers), as they
   // do for the register-heavy median.  B2D_MARCH=0 / 1 forces one of the two (profiling).
+  static const char* strip_env = knob("B2D_STRIP");   // 1: the warp-per-strip kernel (b2d_strip3.cu) where it applies
+  if (strip_env && strip_env[0] == '1' && strip3_supported(kind, filter, s)) return launch_strip3(kind, filter, s, na, st);
   static const char* march_env = knob("B2D_MARCH");
   const bool march = march_env ? march_env[0] == '1' : (kind == NK_NONE && filter != FK_MEDIAN3);
   if (march && march3_supported(s)) return launch_march3(kind, filter, s, na, st);
