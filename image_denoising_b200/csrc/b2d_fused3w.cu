@@ -23,7 +23,14 @@
 
 namespace b2d {
 
-constexpr int FT_THREADS = 256;
+#ifndef B2D_FT_THREADS
+#define B2D_FT_THREADS 256
+#endif
+#ifndef B2D_FT_MINB
+#define B2D_FT_MINB 4
+#endif
+constexpr int FT_THREADS = B2D_FT_THREADS;
+constexpr int FT_STEP = FT_THREADS / 64;   // tile rows per prologue step
 constexpr int FT_TWB = 1024;               // tile width in bytes
 #ifndef B2D_FT_TH
 #define B2D_FT_TH 48
@@ -48,7 +55,7 @@ __device__ __forceinline__ uint2 noise_group(const NoiseArgs& na, int img_local,
 // A4: rows (and image bases) are only 4-byte aligned - rows of 4 (mod 8) bytes, W = 500.  Without a
 // generator (KIND == NK_NONE) groups do not matter, so the same tile code runs with 32-bit accesses.
 template <int KIND, int FILTER, int KW, bool A4 = false>
-__global__ void __launch_bounds__(FT_THREADS, 4) k_fused3(ImageSet s, NoiseArgs na) {
+__global__ void __launch_bounds__(FT_THREADS, B2D_FT_MINB) k_fused3(ImageSet s, NoiseArgs na) {
   static_assert(!A4 || KIND == NK_NONE, "the 4-byte aligned variant has no generator");
   using F = Filter3W<FILTER, KW>;
   constexpr int TPB = FT_TWB / (4 * KW);            // threads per band
@@ -72,7 +79,7 @@ __global__ void __launch_bounds__(FT_THREADS, 4) k_fused3(ImageSet s, NoiseArgs 
       const int nwv = (s.rowbytes - c) >> 2;            // valid words of the thread's 16 bytes
       if (v0) {
 #pragma unroll FT_UNROLL
-        for (int tr = r0; tr < rows; tr += 4) {
+        for (int tr = r0; tr < rows; tr += FT_STEP) {
           int ys = y0 - 1 + tr;
           if (ys < 0 || ys >= s.h) ys = border_map(ys, s.h, F::BORDER);
           const uint32_t* pw = reinterpret_cast<const uint32_t*>(img + (uint32_t)ys * (uint32_t)s.rowbytes + (uint32_t)c);
@@ -96,7 +103,7 @@ __global__ void __launch_bounds__(FT_THREADS, 4) k_fused3(ImageSet s, NoiseArgs 
     } else {
     if (v0) {
 #pragma unroll FT_UNROLL
-      for (int tr = r0; tr < rows; tr += 4) {
+      for (int tr = r0; tr < rows; tr += FT_STEP) {
         int ys = y0 - 1 + tr;                             // only the first / last tile row can leave the image
         if (ys < 0 || ys >= s.h) ys = border_map(ys, s.h, F::BORDER);   // (warp-uniform: a warp shares tr)
         const uint32_t e = (uint32_t)ys * (uint32_t)s.rowbytes + (uint32_t)c;
@@ -226,8 +233,6 @@ cudaError_t launch_march3(int kind, int filter, const ImageSet& s, const NoiseAr
 bool march3_supported(const ImageSet& s);
 bool march3_a4_supported(const ImageSet& s);
 cudaError_t launch_march3_a4(int filter, const ImageSet& s, const NoiseArgs& na, cudaStream_t st);
-bool strip3_supported(int kind, int filter, const ImageSet& s);
-cudaError_t launch_strip3(int kind, int filter, const ImageSet& s, const NoiseArgs& na, cudaStream_t st);
 
 cudaError_t launch_fused3(int kind, int filter, const ImageSet& s, const NoiseArgs& na, cudaStream_t st) {
   if (s.count <= 0) return cudaSuccess;
@@ -256,8 +261,8 @@ cudaError_t launch_fused3(int kind, int filter, const ImageSet& s, const NoiseAr
   // (0.32 / 0.35 ms vs 0.48 / 0.50 ms: no apron rows, register prefetch); with a generator in the
   // prologue the tiles win (0.69 vs 0.78 ms for sap_mean: longer phases, fewer barriers), as they
   // do for the register-heavy median.  B2D_MARCH=0 / 1 forces one of the two (profiling).
-  static const char* strip_env = knob("B2D_STRIP");   // 1: the warp-per-strip kernel (b2d_strip3.cu) where it applies
-  if (strip_env && strip_env[0] == '1' && strip3_supported(kind, filter, s)) return launch_strip3(kind, filter, s, na, st);
+  // (A third schedule - one warp per 512-byte column strip, taps by SHFL, no shared memory and no barrier - was
+  // measured 13-15 % slower than the tiles: profiles/r02q_strip.txt, source in the commit before its removal.)
   static const char* march_env = knob("B2D_MARCH");
   const bool march = march_env ? march_env[0] == '1' : (kind == NK_NONE && filter != FK_MEDIAN3);
   if (march && march3_supported(s)) return launch_march3(kind, filter, s, na, st);
