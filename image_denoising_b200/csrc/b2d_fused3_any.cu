@@ -20,13 +20,22 @@
 namespace b2d {
 
 constexpr int F3_THREADS = 256;
-constexpr int F3_TILE_WB = 1024;                  // tile width in bytes
-constexpr int F3_TILE_H = 48;                     // as the hot kernel: 4 CTAs / SM
+#ifndef B2D_F3ANY_UNROLL
+#define B2D_F3ANY_UNROLL 1
+#endif
+constexpr int F3_UNROLL = B2D_F3ANY_UNROLL;       // prologue steps unrolled (Philox chains of several groups in flight)
 constexpr int F3_APRON = 16;                      // shared bytes each side of the tile (8 are generated, 4 are read)
-constexpr int F3_SROW = F3_TILE_WB + 2 * F3_APRON;
-constexpr int F3_ROWS = F3_TILE_H + 2;
-constexpr int F3_GROUPS_PER_ROW = (F3_TILE_WB + 16) / 8 + 1;  // +1: rows whose start is 4 (mod 8)
-constexpr size_t F3_SMEM = (size_t)F3_ROWS * F3_SROW;
+// Tile = TWB bytes x 49152 / TWB rows (1024 x 48 as the hot kernel, or 512 x 96: VOC's 1500-byte rows fill 3 x 512
+// to 98 % but 2 x 1024 to 73 %); the band height of the filter phase is 12 rows (24 for the median) either way.
+template <int TWB>
+struct F3Geom {
+  static constexpr int TILE_WB = TWB;
+  static constexpr int TILE_H = 49152 / TWB;
+  static constexpr int SROW = TWB + 2 * F3_APRON;
+  static constexpr int ROWS = TILE_H + 2;
+  static constexpr int GROUPS_PER_ROW = (TWB + 16) / 8 + 1;   // +1: rows whose start is 4 (mod 8)
+  static constexpr size_t SMEM = (size_t)ROWS * SROW;
+};
 
 // load the 8 bytes of group g of an image (4-byte aligned base, elems % 4 == 0)
 __device__ __forceinline__ uint2 load_group(const uint8_t* img, uint64_t elems, uint32_t g) {
@@ -46,9 +55,12 @@ __device__ __forceinline__ uint2 load_group(const uint8_t* img, uint64_t elems, 
 // that starts at 4 (mod 8) begins and ends in the middle of a group; the group is generated
 // whole and the half that belongs to the row is kept) - the PACKED operators of the hot kernel.
 // Filter: the band code of k_fused3 (b2d_fused3w.cu), 32-bit stores.
-template <int KIND, int FILTER, int KW>
+template <int KIND, int FILTER, int KW, int TWB>
 __global__ void __launch_bounds__(F3_THREADS, 4) k_fused3_any(ImageSet s, NoiseArgs na) {
   using F = Filter3W<FILTER, KW>;
+  using G = F3Geom<TWB>;
+  constexpr int F3_TILE_WB = G::TILE_WB, F3_TILE_H = G::TILE_H, F3_SROW = G::SROW, F3_ROWS = G::ROWS;
+  constexpr int F3_GROUPS_PER_ROW = G::GROUPS_PER_ROW;
   constexpr int TPB = F3_TILE_WB / (4 * KW);        // threads per band
   constexpr int BANDS = F3_THREADS / TPB;
   constexpr int BAND_H = F3_TILE_H / BANDS;
@@ -75,6 +87,7 @@ __global__ void __launch_bounds__(F3_THREADS, 4) k_fused3_any(ImageSet s, NoiseA
   __syncthreads();
   const uint32_t g_full = (uint32_t)(s.elems >> 3);              // groups that lie completely inside the image
   const bool al8 = (reinterpret_cast<uintptr_t>(img) & 7u) == 0;
+#pragma unroll F3_UNROLL
   for (int it = tid; it < rows_needed * F3_GROUPS_PER_ROW; it += F3_THREADS) {
     const int tr = it / F3_GROUPS_PER_ROW;
     const int gi = it - tr * F3_GROUPS_PER_ROW;
@@ -157,22 +170,31 @@ __global__ void __launch_bounds__(F3_THREADS, 4) k_fused3_any(ImageSet s, NoiseA
   }
 }
 
-template <int KIND, int FILTER>
-static cudaError_t launch_one(const ImageSet& s, const NoiseArgs& na, cudaStream_t st) {
+template <int KIND, int FILTER, int TWB>
+static cudaError_t launch_width(const ImageSet& s, const NoiseArgs& na, cudaStream_t st) {
   constexpr int KW = FILTER == FK_MEDIAN3 ? 2 : 4;
+  using G = F3Geom<TWB>;
   static bool attr_done[64] = {};               // per device: the attribute lives in the context
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_done[dev & 63]) {
-    const cudaError_t e =
-        cudaFuncSetAttribute(k_fused3_any<KIND, FILTER, KW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F3_SMEM);
+    const cudaError_t e = cudaFuncSetAttribute(k_fused3_any<KIND, FILTER, KW, TWB>,
+                                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM);
     if (e != cudaSuccess) return e;
     attr_done[dev & 63] = true;
   }
-  const dim3 grid((s.rowbytes + F3_TILE_WB - 1) / F3_TILE_WB, (s.h + F3_TILE_H - 1) / F3_TILE_H, s.count);
-  k_fused3_any<KIND, FILTER, KW><<<grid, F3_THREADS, F3_SMEM, st>>>(s, na);
+  const dim3 grid((s.rowbytes + G::TILE_WB - 1) / G::TILE_WB, (s.h + G::TILE_H - 1) / G::TILE_H, s.count);
+  k_fused3_any<KIND, FILTER, KW, TWB><<<grid, F3_THREADS, G::SMEM, st>>>(s, na);
   count_launch();
   return cudaGetLastError();
+}
+
+template <int KIND, int FILTER>
+static cudaError_t launch_one(const ImageSet& s, const NoiseArgs& na, cudaStream_t st) {
+  // the width that pads the rows least (ties: the wider tile)
+  const int pad1024 = (s.rowbytes + 1023) / 1024 * 1024, pad512 = (s.rowbytes + 511) / 512 * 512;
+  if (pad512 < pad1024) return launch_width<KIND, FILTER, 512>(s, na, st);
+  return launch_width<KIND, FILTER, 1024>(s, na, st);
 }
 
 template <int KIND>
