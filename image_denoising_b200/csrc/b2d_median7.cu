@@ -12,9 +12,9 @@
 //             smallest / largest have >= 25 core values on one side and are on that side of all four medians.  Marching
 //             down by 2 rows keeps two of the three 12-lists; the merge of two of them (24-list) serves two blocks.
 //   level 2 : survivors + the sorted outer column (20 values): the 6 smallest / largest go the same way -> 8 survivors.
-//   level 3 : survivors + the sorted private row (6 core columns, reused as the next block's new core row, + the corner
-//             inserted) = 15 values: their middle one is the median.
-// 487 min / max instructions per block = 122 per output byte instead of 362 (+ the operand fetches).  All programs are
+//   level 3 : survivors + the sorted private row (its 6 core columns, reused as the next block's new core row) = 14
+//             values, whose two middle ones m6 <= m7 bracket the median of the 15: min(max(corner, m6), m7).
+// 463 min / max instructions per block = 116 per output byte instead of 362 (+ the operand fetches).  All programs are
 // generated and PROVEN (0-1 principle over every sorted input) by scripts/gen_median7_networks.py
 // (b2d_median7_nets.inc); data independent, so they run on the two u16 lanes of a register: lane 0 = the block at byte
 // column c, lane 1 = the block 6 bytes (2 pixels) to the right.  Border: REPLICATE, as OpenCV's medianBlur.
@@ -28,16 +28,23 @@ namespace b2d {
 
 constexpr int S7_XU = 32;                          // 12-byte units (4 pixels: the two lanes' blocks) per tile row
 constexpr int S7_SEGS = 2;                         // vertical segments per tile, one thread each per unit and channel
-constexpr int S7_SEG_H = 16;                       // rows per segment = 8 steps of the march
+constexpr int S7_SEG_H = 24;                       // rows per segment = 12 steps of the march
 constexpr int S7_THREADS = S7_XU * 3 * S7_SEGS;    // 192
 constexpr int S7_TILE_WB = S7_XU * 12;             // 384 bytes
 constexpr int S7_TILE_H = S7_SEGS * S7_SEG_H;      // 32 rows
 constexpr int S7_APRON = 12;                       // >= 9 bytes to the left, 9 beyond the unit to the right; multiple of 4
 constexpr int S7_SROW = S7_TILE_WB + 2 * S7_APRON;
 constexpr int S7_ROWS = S7_TILE_H + 7;             // rows y0 - 3 .. y0 + TILE_H + 3 (the last block reads row y + 4)
-constexpr size_t S7_SMEM = (size_t)S7_ROWS * S7_SROW;
+constexpr size_t S7_TILE_BYTES = (size_t)S7_ROWS * S7_SROW;
+// The lists a step hands to later steps wait in shared memory ([36][threads] words), not in registers: with them the
+// levels 2 / 3 of a step need ~100 registers, and 4 CTAs / SM (80 registers) run 8 % faster than 3.
+//   words 0 .. 23 : Q, the 24-list an even step merges for itself and the odd step after it; once that step has read it,
+//                   words 0 .. 11 take the odd step's new 12-list (the next even step's second list)
+//   words 24 .. 35: the even step's new 12-list (the next even step's first list)
+constexpr int S7_PARK = 36;
+constexpr size_t S7_SMEM = S7_TILE_BYTES + (size_t)S7_PARK * S7_THREADS * 4;
 
-__global__ void __launch_bounds__(S7_THREADS, 2) k_median7_sep(ImageSet s) {
+__global__ void __launch_bounds__(S7_THREADS, 4) k_median7_sep(ImageSet s) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int tid = threadIdx.x;
   const int c0 = blockIdx.x * S7_TILE_WB, y0 = blockIdx.y * S7_TILE_H;
@@ -80,7 +87,9 @@ __global__ void __launch_bounds__(S7_THREADS, 2) k_median7_sep(ImageSet s) {
   const uint8_t* q0 = smem + (seg * S7_SEG_H) * S7_SROW + S7_APRON + 12 * tx + ch;
   auto at = [&](int r, int d) {                     // r: image row ys - 3 + r
     const uint8_t* q = q0 + r * S7_SROW + 3 * d;
-    return __byte_perm((uint32_t)q[0], (uint32_t)q[6], 0x5410);
+    uint32_t v;                                     // lane 1 * 2^16 + lane 0 as an IMAD: the FMA pipe idles, the ALU pipe
+    asm("mad.lo.u32 %0, %1, 65536, %2;" : "=r"(v) : "r"((uint32_t)q[6]), "r"((uint32_t)q[0]));   // is the one that is full
+    return v;
   };
   auto sorted_row = [&](int r, uint32_t (&o)[6]) {  // the 6 core columns d = -2 .. 3 of a row, sorted
     const uint32_t v[6] = {at(r, -2), at(r, -1), at(r, 0), at(r, 1), at(r, 2), at(r, 3)};
@@ -93,13 +102,18 @@ __global__ void __launch_bounds__(S7_THREADS, 2) k_median7_sep(ImageSet s) {
     B2D_NET_PAIR(in, o);
   };
 
-  // warm-up: L0 = rows (ys - 2, ys - 1) = window rows 1, 2; L1 = rows (ys, ys + 1) = window rows 3, 4; and the sorted
-  // row ys + 2 (window row 5), which the first step pairs with row ys + 3
-  uint32_t La[12], Lb[12], Q[24], nxt[6];
+  // warm-up: L0 = rows (ys - 2, ys - 1) = window rows 1, 2 -> words 24..35; L1 = rows (ys, ys + 1) = window rows 3, 4 ->
+  // words 0..11; and the sorted row ys + 2 (window row 5), which the first step pairs with row ys + 3
+  uint32_t nxt[6];
+  uint32_t* const sq = reinterpret_cast<uint32_t*>(smem + S7_TILE_BYTES) + tid;   // this thread's column of parked words
   {
-    uint32_t r1[6], r2[6];
-    sorted_row(1, r1); sorted_row(2, r2); pair_list(r1, r2, La);
-    sorted_row(3, r1); sorted_row(4, r2); pair_list(r1, r2, Lb);
+    uint32_t r1[6], r2[6], L[12];
+    sorted_row(1, r1); sorted_row(2, r2); pair_list(r1, r2, L);
+#pragma unroll
+    for (int i = 0; i < 12; ++i) sq[(24 + i) * S7_THREADS] = L[i];
+    sorted_row(3, r1); sorted_row(4, r2); pair_list(r1, r2, L);
+#pragma unroll
+    for (int i = 0; i < 12; ++i) sq[i * S7_THREADS] = L[i];
     sorted_row(5, nxt);
   }
   uint8_t* out = s.out + (uint64_t)img_local * s.elems + (uint64_t)ys * s.rowbytes + c;
@@ -117,29 +131,32 @@ __global__ void __launch_bounds__(S7_THREADS, 2) k_median7_sep(ImageSet s) {
       pair_list(nxt, r6, Ln);                       // rows (y + 2, y + 3)
     }
     if (even) {
-      // have La = L_k, Lb = L_{k+1}; Q = merge(L_{k+1}, L_{k+2}) serves this block and the next one
-      uint32_t in[24];
+      // lists L_k (words 24..35), L_{k+1} (words 0..11) and the new L_{k+2}; Q = merge(L_{k+1}, L_{k+2}) serves this
+      // block and the next one
+      uint32_t in[24], Q[24];
 #pragma unroll
-      for (int i = 0; i < 12; ++i) { in[i] = Lb[i]; in[12 + i] = Ln[i]; }
+      for (int i = 0; i < 12; ++i) { in[i] = sq[i * S7_THREADS]; in[12 + i] = Ln[i]; }
       B2D_NET_QUAD(in, Q);
+#pragma unroll
+      for (int i = 0; i < 24; ++i) sq[i * S7_THREADS] = Q[i];
       uint32_t in2[36];
 #pragma unroll
-      for (int i = 0; i < 12; ++i) in2[i] = La[i];
+      for (int i = 0; i < 12; ++i) in2[i] = sq[(24 + i) * S7_THREADS];
 #pragma unroll
       for (int i = 0; i < 24; ++i) in2[12 + i] = Q[i];
       B2D_NET_CORE(in2, core);
 #pragma unroll
-      for (int i = 0; i < 12; ++i) La[i] = Ln[i];   // kept: L_{k+2}
+      for (int i = 0; i < 12; ++i) sq[(24 + i) * S7_THREADS] = Ln[i];   // L_{k+2}: first list of the next even step
     } else {
-      // have Q = merge(L_k, L_{k+1}) and La = L_{k+1}; the new list completes the core
+      // Q = merge(L_k, L_{k+1}) is parked; the new list completes the core
       uint32_t in2[36];
 #pragma unroll
       for (int i = 0; i < 12; ++i) in2[i] = Ln[i];
 #pragma unroll
-      for (int i = 0; i < 24; ++i) in2[12 + i] = Q[i];
+      for (int i = 0; i < 24; ++i) in2[12 + i] = sq[i * S7_THREADS];
       B2D_NET_CORE(in2, core);
 #pragma unroll
-      for (int i = 0; i < 12; ++i) Lb[i] = Ln[i];   // next (even) step: La = L_{k+1}, Lb = L_{k+2}
+      for (int i = 0; i < 12; ++i) sq[i * S7_THREADS] = Ln[i];          // L_{k+2}: second list of the next even step
     }
     // level 2: outer columns d = -3 (left outputs) and d = 4 (right outputs) over the core rows wr + 1 .. wr + 6
     uint32_t sl[8], sr[8];
@@ -162,17 +179,13 @@ __global__ void __launch_bounds__(S7_THREADS, 2) k_median7_sep(ImageSet s) {
     // level 3: private rows wr (top outputs) and wr + 7 (bottom outputs)
     uint32_t res[4];                                // (x, y), (x+1, y), (x, y+1), (x+1, y+1)
     auto finish = [&](const uint32_t (&row6)[6], uint32_t corner, const uint32_t (&surv)[8]) -> uint32_t {
-      uint32_t in7[7], row7[7], in15[15], m[1];
+      uint32_t in14[14], m[2];
 #pragma unroll
-      for (int i = 0; i < 6; ++i) in7[i] = row6[i];
-      in7[6] = corner;
-      B2D_NET_INS(in7, row7);
+      for (int i = 0; i < 8; ++i) in14[i] = surv[i];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) in15[i] = surv[i];
-#pragma unroll
-      for (int i = 0; i < 7; ++i) in15[8 + i] = row7[i];
-      B2D_NET_MED(in15, m);
-      return m[0];
+      for (int i = 0; i < 6; ++i) in14[8 + i] = row6[i];
+      B2D_NET_MID2(in14, m);                        // the two middle values of the 14
+      return VMIN(VMAX(corner, m[0]), m[1]);        // ... and the 15th value between, below or above them
     };
     {
       uint32_t t6[6];

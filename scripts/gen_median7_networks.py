@@ -8,8 +8,8 @@ The scheme (per 2 x 2 block of outputs, all lists sorted, see b2d_median7.cu for
   QUAD   : two 12-lists -> one sorted 24-list                              (merge 12 + 12)
   CORE   : 12-list + 24-list -> ranks 11..24 of the 36 core values         (pruned merge 12 + 24)
   ROW    : 14 survivors + sorted 6 outer-row values -> ranks 6..13 of 20   (pruned merge 14 + 6)
-  INS    : sorted 6 + 1 value -> sorted 7                                  (merge 6 + 1)
-  MED    : 8 survivors + sorted 7-column -> rank 7 of 15 = the median      (pruned merge 8 + 7)
+  MID2   : 8 survivors + sorted 6 core values of the private row -> ranks 6, 7 of 14 (pruned merge 8 + 6); the median of
+           those 14 and the row's corner value c is min(max(c, m6), m7)
   SORT6  : Bose-Nelson sorting network for 6 values (12 compare-exchanges)
 A program is a list of (op, dst, a, b): op 'min' / 'max' on value numbers (SSA), inputs are values 0 .. n_in - 1."""
 import itertools
@@ -170,8 +170,7 @@ def main():
         "QUAD": ((12, 12), list(range(24))),
         "CORE": ((12, 24), list(range(11, 25))),
         "ROW": ((14, 6), list(range(6, 14))),
-        "INS": ((6, 1), list(range(7))),
-        "MED": ((8, 7), [7]),
+        "MID2": ((8, 6), [6, 7]),
     }
     for name, (sizes, ranks) in specs.items():
         q, outs = build(sizes, ranks)
@@ -181,7 +180,7 @@ def main():
         print("%-6s %3d inputs  %3d ops" % (name, q.n_in, count(q)))
     n = {k: count(v[0]) for k, v in nets.items()}
     per_block = (2 * n["SORT6"] + n["PAIR"]) + n["QUAD"] / 2 + n["CORE"] + 2 * (n["SORT6"] + n["ROW"]) + \
-        2 * (n["SORT6"] + 2 * n["INS"] + 2 * n["MED"]) - n["SORT6"]
+        2 * (n["SORT6"] + 2 * (n["MID2"] + 2)) - n["SORT6"]
     print("min / max operations per 2 x 2 block: %.0f = %.1f per output (forgetful selection: 2 x 181)" %
           (per_block, per_block / 4))
     # whole scheme on random blocks against the plain median
@@ -201,8 +200,8 @@ def main():
             surv = run("ROW", core + outer)
             for ox in (0, 1):
                 pc = 0 if ox == 0 else 7
-                col7 = run("INS", cols[pc] + [img[0 if oy == 0 else 7][pc]])
-                med = run("MED", surv + col7)[0]
+                m6, m7 = run("MID2", surv + cols[pc])
+                med = min(max(img[0 if oy == 0 else 7][pc], m6), m7)
                 win = sorted(img[r][c] for r in range(oy, oy + 7) for c in range(ox, ox + 7))
                 assert med == win[24], (trial, oy, ox)
     print("scheme verified on 300 random 8 x 8 neighbourhoods")
