@@ -326,8 +326,8 @@ def config_roofline(kind, mpix, ms, per_gpu, peak_gbs, peak_src):
         return {"bound": "latency", "achieved": gbs, "peak": peak_gbs, "unit": "GB/s", "frac": gbs / peak_gbs,
                 "note": "16 images = 624 CTAs, barely one wave of 148 SMs x 4: a launch-latency measurement, not a throughput one"}
     return {"bound": "int issue (selection networks)", "frac": None,
-            "note": "k_median_blocks<7>: ALU pipe 92.9 % (profiles/r01e_median7_blocks_full_raw.csv), 181 compare-exchanges "
-                    "per output byte; the four pre-passes are HBM / fp64-scan bound"}
+            "note": "k_median7_sep (sorted rows merged, 116 min / max per output byte instead of 362): ALU pipe 80 % "
+                    "(profiles/r02y_median7_sep_full_raw.csv); the four pre-passes are HBM / fp64-scan bound"}
 
 
 def run_config(cx, cfg, shard_it, steps, peak_gbs, peak_src):

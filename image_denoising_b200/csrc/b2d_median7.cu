@@ -57,9 +57,11 @@ __global__ void __launch_bounds__(S7_THREADS, 4) k_median7_sep(ImageSet s) {
     const int y = min(max(y0 - 3 + tr, 0), s.h - 1);
     const uint8_t* row = img + (uint64_t)y * s.rowbytes;
     const int c = c0 - S7_APRON + 4 * wc;
-    uint32_t w;
+    uint8_t* dst = smem + tr * S7_SROW + 4 * wc;
     if (c >= 0 && c + 4 <= s.rowbytes && ((reinterpret_cast<uintptr_t>(row + c) & 3u) == 0)) {
-      w = __ldg(reinterpret_cast<const uint32_t*>(row + c));
+      // straight to shared memory: every word of the tile in flight at once, nothing waits in registers
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(row + c)
+                   : "memory");
     } else {                                        // clamp the pixel, keep the channel
       uint32_t b[4];
 #pragma unroll
@@ -70,10 +72,10 @@ __global__ void __launch_bounds__(S7_THREADS, 4) k_median7_sep(ImageSet s) {
         px = min(max(px, 0), s.w - 1);
         b[k] = __ldg(row + px * 3 + ch);
       }
-      w = pack4(b[0], b[1], b[2], b[3]);
+      *reinterpret_cast<uint32_t*>(dst) = pack4(b[0], b[1], b[2], b[3]);
     }
-    *reinterpret_cast<uint32_t*>(smem + tr * S7_SROW + 4 * wc) = w;
   }
+  asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
   __syncthreads();
 
   // thread = (segment, channel, unit): a warp shares segment and channel, its lanes are 32 units (12-byte stride: the
