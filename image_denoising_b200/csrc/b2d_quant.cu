@@ -186,30 +186,84 @@ __global__ void k_quant_palette(ImageSet s, int k, const double* centres, uint32
 }
 
 // ---------------------------------------------------------------- apply --
-__global__ void __launch_bounds__(256) k_quant_apply(ImageSet s, int k, const double* centres, const uint32_t* palette) {
-  __shared__ uint16_t s_gam[256], s_cb[3072];
-  __shared__ double cen[QK_MAX][3];
-  __shared__ uint32_t pal[QK_MAX];
-  const int img_local = image_of(s, blockIdx.z);
-  if (threadIdx.x < k * 3) (&cen[0][0])[threadIdx.x] = centres[(size_t)img_local * QK_MAX * 3 + threadIdx.x];
-  if (threadIdx.x < k) pal[threadIdx.x] = palette[(size_t)img_local * QK_MAX + threadIdx.x];
-  stage_tables(s_gam, s_cb);
-  const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
-  uint8_t* out = s.out + (uint64_t)img_local * s.elems;
-  const int npix = s.h * s.w;
-  for (int p = blockIdx.x * 256 + threadIdx.x; p < npix; p += gridDim.x * 256) {
-    const uint8_t* px = img + (size_t)p * 3;
-    const uint32_t lab = lab_forward(px[0], px[1], px[2], s_gam, s_cb);
+// label of one pixel (packed Lab) -> palette colour.  The label is the argmin of the float64 distances in NumPy's
+// operation order - but 66 fp64 operations per pixel made the kernel fp64-pipe bound (2.6 ms per 512 images), and
+// fp32 distances from shared memory still cost 14 instructions per centre.  Here fp32 SCORES decide first:
+// |x - c|^2 - |x|^2 = |c|^2 - 2 x.c, three FFMAs on one LDS.128 per centre.  For x in [0, 255]^3 and centres inside
+// [-512, 512]^3 a score is off by < 0.09 (rounding of the products / sums, of -2c and |c|^2 to fp32), so when the
+// runner-up is more than 0.25 behind, the fp32 winner IS the float64 argmin; the pixels that sit nearly midway between
+// two centres (< 1 %) take the exact loop.
+__device__ __forceinline__ uint32_t quant_colour(uint32_t lab, int k, const float4* sc, const double (*cen)[3],
+                                                 const uint32_t* pal, int wild) {
+  const float f0 = (float)(lab & 255u), f1 = (float)((lab >> 8) & 255u), f2 = (float)((lab >> 16) & 255u);
+  int best = 0;
+  float b1 = 3.0e38f, b2 = 3.0e38f;                // smallest and second smallest score
+  for (int c = 0; c < k; ++c) {
+    const float4 m = sc[c];                        // (-2 c0, -2 c1, -2 c2, |c|^2)
+    const float d = fmaf(f0, m.x, fmaf(f1, m.y, fmaf(f2, m.z, m.w)));
+    if (d < b1) { b2 = b1; b1 = d; best = c; }
+    else b2 = fminf(b2, d);
+  }
+  if (wild || !(b2 - b1 > 0.25f)) {
     const double x0 = (double)(lab & 255u), x1 = (double)((lab >> 8) & 255u), x2 = (double)((lab >> 16) & 255u);
-    int best = 0;
     double bd = 0.0;
+    best = 0;
     for (int c = 0; c < k; ++c) {
       // ((x - c) ** 2).sum(-1): products and sums rounded separately, left to right (no FMA)
       const double d0 = __dsub_rn(x0, cen[c][0]), d1 = __dsub_rn(x1, cen[c][1]), d2 = __dsub_rn(x2, cen[c][2]);
       const double d = __dadd_rn(__dadd_rn(__dmul_rn(d0, d0), __dmul_rn(d1, d1)), __dmul_rn(d2, d2));
       if (c == 0 || d < bd) { bd = d; best = c; }       // np.argmin: first minimum
     }
-    const uint32_t q = pal[best];
+  }
+  return pal[best];
+}
+
+__global__ void __launch_bounds__(256) k_quant_apply(ImageSet s, int k, const double* centres, const uint32_t* palette) {
+  __shared__ uint16_t s_gam[256], s_cb[3072];
+  __shared__ double cen[QK_MAX][3];
+  __shared__ float4 sc[QK_MAX];
+  __shared__ uint32_t pal[QK_MAX];
+  __shared__ int s_wild;                           // an (injected) centre far outside the uint8 cube: exact loop only
+  const int img_local = image_of(s, blockIdx.z);
+  if (threadIdx.x == 0) s_wild = 0;
+  __syncthreads();
+  if (threadIdx.x < k * 3) {
+    const double c = centres[(size_t)img_local * QK_MAX * 3 + threadIdx.x];
+    (&cen[0][0])[threadIdx.x] = c;
+    if (!(fabs(c) <= 512.0)) s_wild = 1;
+  }
+  if (threadIdx.x < k) {
+    const double* c = centres + ((size_t)img_local * QK_MAX + threadIdx.x) * 3;
+    sc[threadIdx.x] = make_float4((float)(-2.0 * c[0]), (float)(-2.0 * c[1]), (float)(-2.0 * c[2]),
+                                  (float)(c[0] * c[0] + c[1] * c[1] + c[2] * c[2]));
+    pal[threadIdx.x] = palette[(size_t)img_local * QK_MAX + threadIdx.x];
+  }
+  stage_tables(s_gam, s_cb);
+  const int wild = s_wild;
+  const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
+  uint8_t* out = s.out + (uint64_t)img_local * s.elems;
+  const int npix = s.h * s.w;
+  auto one = [&](uint32_t b, uint32_t g, uint32_t r) {
+    return quant_colour(lab_forward(b, g, r, s_gam, s_cb), k, sc, cen, pal, wild);
+  };
+  // four pixels = three words per thread and step when the image is word aligned
+  const bool words = ((reinterpret_cast<uintptr_t>(img) | reinterpret_cast<uintptr_t>(out)) & 3u) == 0;
+  const int nquad = words ? npix / 4 : 0;
+  for (int q = blockIdx.x * 256 + threadIdx.x; q < nquad; q += gridDim.x * 256) {
+    const uint32_t* pw = reinterpret_cast<const uint32_t*>(img) + (size_t)q * 3;
+    const uint32_t w0 = __ldg(pw), w1 = __ldg(pw + 1), w2 = __ldg(pw + 2);
+    const uint32_t q0 = one(w0 & 255u, (w0 >> 8) & 255u, (w0 >> 16) & 255u);
+    const uint32_t q1 = one(w0 >> 24, w1 & 255u, (w1 >> 8) & 255u);
+    const uint32_t q2 = one((w1 >> 16) & 255u, w1 >> 24, w2 & 255u);
+    const uint32_t q3 = one((w2 >> 8) & 255u, (w2 >> 16) & 255u, w2 >> 24);
+    uint32_t* ow = reinterpret_cast<uint32_t*>(out) + (size_t)q * 3;
+    ow[0] = q0 | (q1 << 24);
+    ow[1] = (q1 >> 8) | (q2 << 16);
+    ow[2] = (q2 >> 16) | (q3 << 8);
+  }
+  for (int p = 4 * nquad + blockIdx.x * 256 + threadIdx.x; p < npix; p += gridDim.x * 256) {
+    const uint8_t* px = img + (size_t)p * 3;
+    const uint32_t q = one(px[0], px[1], px[2]);
     uint8_t* o = out + (size_t)p * 3;
     o[0] = (uint8_t)q; o[1] = (uint8_t)(q >> 8); o[2] = (uint8_t)(q >> 16);
   }
@@ -242,7 +296,9 @@ int run_quant(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, uint8_t*
   count_launch();
   k_quant_palette<<<s.count, QK_MAX, 0, st>>>(s, k, centres, palette);
   count_launch();
-  const unsigned bx = (unsigned)std::min<size_t>(((size_t)p.h * p.w + 255) / 256, 148 * 4);
+  // every CTA stages 6.6 KB of Lab tables first: as few CTAs per image as still fill the GPU (16 per SM over the batch)
+  const size_t want = ((size_t)sm_count() * 16 + (size_t)s.count - 1) / (size_t)s.count;
+  const unsigned bx = (unsigned)std::max<size_t>(1, std::min<size_t>(((size_t)p.h * p.w + 255) / 256, std::min<size_t>(want, 148 * 4)));
   k_quant_apply<<<dim3(bx, 1, s.count), 256, 0, st>>>(s, k, centres, palette);
   count_launch();
   const cudaError_t e = cudaGetLastError();
