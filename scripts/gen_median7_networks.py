@@ -206,15 +206,25 @@ def main():
                 assert med == win[24], (trial, oy, ox)
     print("scheme verified on 300 random 8 x 8 neighbourhoods")
     if len(sys.argv) > 1 and sys.argv[1] == "--write":
-        path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "image_denoising_b200", "csrc",
-                            "b2d_median7_nets.inc")
-        with open(path, "w") as f:
-            f.write("// GENERATED by scripts/gen_median7_networks.py - do not edit.  Merge / selection programs of the separable\n"
-                    "// 7 x 7 median: every program is proven there (0-1 principle over all sorted inputs) before it is written.\n"
-                    "// VMIN / VMAX are defined by the including file (u16x2 minimum / maximum).\n\n")
-            for name, (q, outs) in nets.items():
-                emit(name, q, outs, f)
-        print("wrote", path)
+        with open(INC_PATH, "w") as f:
+            f.write(render(nets))
+        print("wrote", INC_PATH)
+    return nets
+
+
+INC_PATH = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "image_denoising_b200", "csrc",
+                        "b2d_median7_nets.inc")
+
+
+def render(nets):
+    import io
+    f = io.StringIO()
+    f.write("// GENERATED by scripts/gen_median7_networks.py - do not edit.  Merge / selection programs of the separable\n"
+            "// 7 x 7 median: every program is proven there (0-1 principle over all sorted inputs) before it is written.\n"
+            "// VMIN / VMAX are defined by the including file (u16x2 minimum / maximum).\n\n")
+    for name, (q, outs) in nets.items():
+        emit(name, q, outs, f)
+    return f.getvalue()
 
 
 if __name__ == "__main__":
