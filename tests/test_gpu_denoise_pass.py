@@ -12,7 +12,11 @@ pytestmark = pytest.mark.gpu
 SHAPES = [(64, 96), (375, 500), (37, 53), (17, 344), (5, 7), (600, 1000)]
 
 
-@pytest.mark.parametrize("shape", SHAPES)
+# the separable 7 x 7 kernel's tiles are 384 bytes x 48 rows, segments of 24 rows, steps of 2: sizes at and around them
+MEDIAN_SHAPES = SHAPES + [(1, 1), (3, 2), (49, 129), (97, 256), (24, 128), (25, 131), (47, 127)]
+
+
+@pytest.mark.parametrize("shape", MEDIAN_SHAPES)
 @pytest.mark.parametrize("k", [5, 7])
 def test_median_k_bit_exact(cuda, shape, k):
     from image_denoising_b200 import api
