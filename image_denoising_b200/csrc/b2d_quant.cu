@@ -70,21 +70,26 @@ __device__ __forceinline__ void stage_tables(uint16_t* s_gam, uint16_t* s_cb) {
 }
 
 // ------------------------------------------------------------------ fit --
-__global__ void __launch_bounds__(256) k_quant_fit(ImageSet s, int k, uint32_t k0, uint32_t k1, uint64_t first_global,
-                                                   double* centres /* [batch][QK_MAX][3] */) {
+// One CTA of 512 threads per image (at 128 images per GPU - a C5 shard at N = 8 - the kernel's time is ONE CTA's latency).
+constexpr int QF_THREADS = 512;
+constexpr int QF_PER = Q_SAMPLES / QF_THREADS;   // samples per thread
+
+__global__ void __launch_bounds__(QF_THREADS) k_quant_fit(ImageSet s, int k, uint32_t k0, uint32_t k1, uint64_t first_global,
+                                                          double* centres /* [batch][QK_MAX][3] */) {
   __shared__ uint16_t s_gam[256], s_cb[3072];
   __shared__ uint32_t smp[Q_SAMPLES];            // L | a << 8 | b << 16
-  __shared__ float mind[Q_SAMPLES];
+  __shared__ float mind[Q_SAMPLES];              // seeding: min distance^2; Lloyd: the warps' partial sums (wpart)
   __shared__ float cen[QK_MAX][3];
+  __shared__ float4 sc4[QK_MAX];                 // (-2 c, |c|^2): argmin |x - c|^2 = argmin (|c|^2 - 2 x.c)
   __shared__ unsigned int sums[QK_MAX][4];       // integer sums: deterministic accumulation
-  __shared__ float part[256];
+  __shared__ float part[QF_THREADS];
   stage_tables(s_gam, s_cb);
   const int tid = threadIdx.x;
   const int img_local = image_of(s, blockIdx.x);
   const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
   const uint64_t gi = first_global + (uint64_t)img_local;
   const uint32_t npix = (uint32_t)(s.h * s.w);
-  for (int i = tid; i < Q_SAMPLES / 4; i += 256) {
+  for (int i = tid; i < Q_SAMPLES / 4; i += QF_THREADS) {
     const uint4 r = philox4x32((uint32_t)i, 0xC0u, (uint32_t)gi, (uint32_t)(gi >> 32), k0, k1);
     const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
@@ -106,17 +111,20 @@ __global__ void __launch_bounds__(256) k_quant_fit(ImageSet s, int k, uint32_t k
     const uint32_t v = smp[ru.x % Q_SAMPLES];
     cen[0][0] = (float)(v & 255u); cen[0][1] = (float)((v >> 8) & 255u); cen[0][2] = (float)((v >> 16) & 255u);
   }
-  for (int i = tid; i < Q_SAMPLES; i += 256) mind[i] = 3.0e38f;
+  for (int i = tid; i < Q_SAMPLES; i += QF_THREADS) mind[i] = 3.0e38f;
   __syncthreads();
   for (int c = 1; c < k; ++c) {
-    float loc = 0.f;
-    for (int j = 0; j < Q_SAMPLES / 256; ++j) {          // thread owns a contiguous run of samples
-      const int i = tid * (Q_SAMPLES / 256) + j;
-      const float d = fminf(mind[i], dist2(smp[i], c - 1));
-      mind[i] = d;
-      loc += d;
+    // a run of 16 consecutive samples per partial sum (threads 0 .. 255; the draw below walks runs, then samples)
+    if (tid < 256) {
+      float loc = 0.f;
+      for (int j = 0; j < Q_SAMPLES / 256; ++j) {
+        const int i = tid * (Q_SAMPLES / 256) + j;
+        const float d = fminf(mind[i], dist2(smp[i], c - 1));
+        mind[i] = d;
+        loc += d;
+      }
+      part[tid] = loc;
     }
-    part[tid] = loc;
     __syncthreads();
     if (tid == 0) {
       float tot = 0.f;
@@ -133,22 +141,53 @@ __global__ void __launch_bounds__(256) k_quant_fit(ImageSet s, int k, uint32_t k
     }
     __syncthreads();
   }
-  // ---- Lloyd iterations on the sample
+  // ---- Lloyd iterations on the sample.  A thread labels its samples in registers by the fp32 score |c|^2 - 2 x.c (one
+  // LDS.128 + 3 FFMA per centre); every centre's integer sums (deterministic in any order) are then reduced inside the warp
+  // (REDUX) and across the warps through shared memory.  Round 1: 3 LDS + 3 I2F + 8 more per distance, and 4 shared
+  // atomicAdds per sample on k x 4 addresses.
+  unsigned int (*wpart)[QK_MAX][4] = reinterpret_cast<unsigned int (*)[QK_MAX][4]>(mind);   // [QF_THREADS / 32][QK_MAX][4]
+  static_assert(sizeof(unsigned int) * (QF_THREADS / 32) * QK_MAX * 4 <= sizeof(float) * Q_SAMPLES, "wpart fits in mind");
+  const int lane = tid & 31, wid = tid >> 5;
   for (int it = 0; it < Q_ITERS; ++it) {
-    for (int i = tid; i < QK_MAX * 4; i += 256) (&sums[0][0])[i] = 0u;
+    if (tid < k)
+      sc4[tid] = make_float4(-2.0f * cen[tid][0], -2.0f * cen[tid][1], -2.0f * cen[tid][2],
+                             cen[tid][0] * cen[tid][0] + cen[tid][1] * cen[tid][1] + cen[tid][2] * cen[tid][2]);
     __syncthreads();
-    for (int i = tid; i < Q_SAMPLES; i += 256) {
-      const uint32_t v = smp[i];
+    uint32_t lab[QF_PER];
+    unsigned long long pk[QF_PER];                 // L | a << 12 | b << 24 | 1 << 36: one 64-bit add per sample and centre
+#pragma unroll
+    for (int j = 0; j < QF_PER; ++j) {
+      const uint32_t v = smp[tid + QF_THREADS * j];
+      const uint32_t L = v & 255u, a = (v >> 8) & 255u, b = (v >> 16) & 255u;
+      const float f0 = (float)L, f1 = (float)a, f2 = (float)b;
       int best = 0;
-      float bd = dist2(v, 0);
-      for (int c = 1; c < k; ++c) {
-        const float d = dist2(v, c);
+      float bd = 3.0e38f;
+      for (int c = 0; c < k; ++c) {
+        const float4 m = sc4[c];
+        const float d = fmaf(f0, m.x, fmaf(f1, m.y, fmaf(f2, m.z, m.w)));
         if (d < bd) { bd = d; best = c; }
       }
-      atomicAdd(&sums[best][0], v & 255u);
-      atomicAdd(&sums[best][1], (v >> 8) & 255u);
-      atomicAdd(&sums[best][2], (v >> 16) & 255u);
-      atomicAdd(&sums[best][3], 1u);
+      lab[j] = (uint32_t)best;
+      pk[j] = (unsigned long long)L | ((unsigned long long)a << 12) | ((unsigned long long)b << 24) | (1ull << 36);
+    }
+    for (int c = 0; c < k; ++c) {
+      unsigned long long acc = 0ull;
+#pragma unroll
+      for (int j = 0; j < QF_PER; ++j)
+        if (lab[j] == (uint32_t)c) acc += pk[j];
+      const unsigned int a0 = __reduce_add_sync(0xffffffffu, (unsigned int)(acc & 0xfffu));
+      const unsigned int a1 = __reduce_add_sync(0xffffffffu, (unsigned int)((acc >> 12) & 0xfffu));
+      const unsigned int a2 = __reduce_add_sync(0xffffffffu, (unsigned int)((acc >> 24) & 0xfffu));
+      const unsigned int n = __reduce_add_sync(0xffffffffu, (unsigned int)(acc >> 36));
+      if (lane == 0) { wpart[wid][c][0] = a0; wpart[wid][c][1] = a1; wpart[wid][c][2] = a2; wpart[wid][c][3] = n; }
+    }
+    __syncthreads();
+    if (tid < k * 4) {
+      const int c = tid >> 2, x = tid & 3;
+      unsigned int t = 0u;
+#pragma unroll
+      for (int w = 0; w < QF_THREADS / 32; ++w) t += wpart[w][c][x];
+      sums[c][x] = t;
     }
     __syncthreads();
     if (tid < k && sums[tid][3]) {
@@ -292,7 +331,7 @@ int run_quant(const b2d_plan& p, const b2d_spec& sp, const ImageSet& s, uint8_t*
   double* centres = reinterpret_cast<double*>(tables);
   uint32_t* palette = reinterpret_cast<uint32_t*>(tables + (size_t)p.n * QK_MAX * 3 * sizeof(double));
   if (fields && fields->f0) k_quant_take<<<s.count, 128, 0, st>>>(s, k, fields->f0, centres);
-  else k_quant_fit<<<s.count, 256, 0, st>>>(s, k, (uint32_t)seed, (uint32_t)(seed >> 32), first_global, centres);
+  else k_quant_fit<<<s.count, QF_THREADS, 0, st>>>(s, k, (uint32_t)seed, (uint32_t)(seed >> 32), first_global, centres);
   count_launch();
   k_quant_palette<<<s.count, QK_MAX, 0, st>>>(s, k, centres, palette);
   count_launch();
