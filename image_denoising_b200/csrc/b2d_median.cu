@@ -405,13 +405,15 @@ static cudaError_t launch_median_t(const ImageSet& s, cudaStream_t st) {
 }
 
 cudaError_t launch_median7_sep(const ImageSet& s, cudaStream_t st);     // b2d_median7.cu
+cudaError_t launch_median5_sep(const ImageSet& s, cudaStream_t st);
 
 cudaError_t launch_median_k(const ImageSet& s, int k, cudaStream_t st) {
   if (s.count <= 0) return cudaSuccess;
-  // B2D_MEDIAN_MODE = 1: one output at a time, 2: horizontal pairs, 3: 2 x 2 blocks by forgetful selection (the default
-  // for k = 5); default for k = 7: 2 x 2 blocks by merging sorted rows (b2d_median7.cu)  (measurement knob)
+  // B2D_MEDIAN_MODE = 1: one output at a time, 2: horizontal pairs, 3: 2 x 2 blocks by forgetful selection; default:
+  // 2 x 2 blocks by merging sorted rows (b2d_median7.cu)  (measurement knob)
   static const int mode = [] { const char* e = knob("B2D_MEDIAN_MODE"); return e ? atoi(e) : 0; }();
   if (k == 7 && mode == 0) return launch_median7_sep(s, st);
+  if (k == 5 && mode == 0) return launch_median5_sep(s, st);
   if (k == 5) return mode == 1 ? launch_median_t<5>(s, st) : mode == 2 ? launch_median_pairs<5>(s, st) : launch_median_blocks<5>(s, st);
   if (k == 7) return mode == 1 ? launch_median_t<7>(s, st) : mode == 2 ? launch_median_pairs<7>(s, st) : launch_median_blocks<7>(s, st);
   return cudaErrorInvalidValue;

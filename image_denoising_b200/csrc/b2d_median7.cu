@@ -1,4 +1,5 @@
-// b2d_median7.cu - cv2.medianBlur(u8, 7) (BASELINE config 5), SEPARABLE version: sorted rows are merged, not re-sorted.
+// b2d_median7.cu - cv2.medianBlur(u8, 7) (BASELINE config 5) and (u8, 5), SEPARABLE versions: sorted rows are merged, not
+// re-sorted.  The 7 x 7 kernel is described here, the 5 x 5 one (same scheme, smaller lists) further down.
 //
 // The selection-network kernels of b2d_median.cu ("forgetful selection", 2 x 2 output blocks) start every block from
 // 36 unsorted values: 181 compare-exchanges = 362 min / max instructions per output byte, and the ALU pipe that runs them is
@@ -44,17 +45,12 @@ constexpr size_t S7_TILE_BYTES = (size_t)S7_ROWS * S7_SROW;
 constexpr int S7_PARK = 36;
 constexpr size_t S7_SMEM = S7_TILE_BYTES + (size_t)S7_PARK * S7_THREADS * 4;
 
-__global__ void __launch_bounds__(S7_THREADS, 4) k_median7_sep(ImageSet s) {
-  extern __shared__ __align__(16) uint8_t smem[];
+// tile + apron -> shared memory, REPLICATE at the image border (tile row tr = image row ytop + tr); the caller syncs
+__device__ __forceinline__ void load_tile(uint8_t* smem, const ImageSet& s, const uint8_t* img, int c0, int ytop, int rows) {
   const int tid = threadIdx.x;
-  const int c0 = blockIdx.x * S7_TILE_WB, y0 = blockIdx.y * S7_TILE_H;
-  const int img_local = image_of(s, blockIdx.z);
-  const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
-
-  // ---- tile + apron -> shared memory, REPLICATE at the image border (tile row tr = image row y0 - 3 + tr) ----
-  for (int it = tid; it < S7_ROWS * (S7_SROW / 4); it += S7_THREADS) {
+  for (int it = tid; it < rows * (S7_SROW / 4); it += S7_THREADS) {
     const int tr = it / (S7_SROW / 4), wc = it - tr * (S7_SROW / 4);
-    const int y = min(max(y0 - 3 + tr, 0), s.h - 1);
+    const int y = min(max(ytop + tr, 0), s.h - 1);
     const uint8_t* row = img + (uint64_t)y * s.rowbytes;
     const int c = c0 - S7_APRON + 4 * wc;
     uint8_t* dst = smem + tr * S7_SROW + 4 * wc;
@@ -76,6 +72,16 @@ __global__ void __launch_bounds__(S7_THREADS, 4) k_median7_sep(ImageSet s) {
     }
   }
   asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
+
+__global__ void __launch_bounds__(S7_THREADS, 4) k_median7_sep(ImageSet s) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int tid = threadIdx.x;
+  const int c0 = blockIdx.x * S7_TILE_WB, y0 = blockIdx.y * S7_TILE_H;
+  const int img_local = image_of(s, blockIdx.z);
+  const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
+
+  load_tile(smem, s, img, c0, y0 - 3, S7_ROWS);
   __syncthreads();
 
   // thread = (segment, channel, unit): a warp shares segment and channel, its lanes are 32 units (12-byte stride: the
@@ -215,6 +221,122 @@ __global__ void __launch_bounds__(S7_THREADS, 4) k_median7_sep(ImageSet s) {
     step(k, true);
     if (k + 1 < nsteps) step(k + 1, false);
   }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// The same scheme for cv2.medianBlur(u8, 5): core 4 x 4 (rows y-1 .. y+2, columns x-1 .. x+2) = two row pairs, so a step
+// merges the pair it kept with the new one (16 -> middle 10), adds the sorted outer column (14 -> 6) and the sorted
+// private row (10 -> two middle values + corner).  232 min / max per block = 58 per output byte (forgetful selection: 158).
+// Tile row tr = image row y0 - 2 + tr; the state (one 8-list, one sorted row) stays in registers.
+constexpr int S5_ROWS = S7_TILE_H + 5;
+
+__global__ void __launch_bounds__(S7_THREADS, 5) k_median5_sep(ImageSet s) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int tid = threadIdx.x;
+  const int c0 = blockIdx.x * S7_TILE_WB, y0 = blockIdx.y * S7_TILE_H;
+  const int img_local = image_of(s, blockIdx.z);
+  const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
+  load_tile(smem, s, img, c0, y0 - 2, S5_ROWS);
+  __syncthreads();
+  const int tx = tid & 31, ch = (tid >> 5) % 3, seg = tid / 96;
+  const int c = c0 + 12 * tx + ch;
+  if (12 * tx + c0 >= s.rowbytes) return;
+  const int ys = y0 + seg * S7_SEG_H;
+  if (ys >= s.h) return;
+  const uint8_t* q0 = smem + (seg * S7_SEG_H) * S7_SROW + S7_APRON + 12 * tx + ch;
+  auto at = [&](int r, int d) {                     // window row r = image row ys - 2 + r, column offset d pixels
+    const uint8_t* q = q0 + r * S7_SROW + 3 * d;
+    uint32_t v;
+    asm("mad.lo.u32 %0, %1, 65536, %2;" : "=r"(v) : "r"((uint32_t)q[6]), "r"((uint32_t)q[0]));
+    return v;
+  };
+  auto sorted_row = [&](int r, uint32_t (&o)[4]) {  // the 4 core columns d = -1 .. 2 of a row, sorted
+    const uint32_t v[4] = {at(r, -1), at(r, 0), at(r, 1), at(r, 2)};
+    B2D_NET_SORT4(v, o);
+  };
+  auto pair_list = [&](const uint32_t (&a)[4], const uint32_t (&b)[4], uint32_t (&o)[8]) {
+    uint32_t in[8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { in[i] = a[i]; in[4 + i] = b[i]; }
+    B2D_NET_PAIR5(in, o);
+  };
+  uint32_t Lp[8], nxt[4];                           // rows (y-1, y) merged; row y+1 sorted
+  {
+    uint32_t r1[4], r2[4];
+    sorted_row(1, r1); sorted_row(2, r2); pair_list(r1, r2, Lp);
+    sorted_row(3, nxt);
+  }
+  uint8_t* out = s.out + (uint64_t)img_local * s.elems + (uint64_t)ys * s.rowbytes + c;
+  const int nrows = min(S7_SEG_H, s.h - ys);
+  const bool v0 = c < s.rowbytes, v1 = c + 3 < s.rowbytes, v2 = c + 6 < s.rowbytes, v3 = c + 9 < s.rowbytes;
+  const int nsteps = (nrows + 1) / 2;
+  for (int k = 0; k < nsteps; ++k) {
+    const int wr = 2 * k;                           // window rows wr .. wr + 5 = image rows y-2 .. y+3
+    uint32_t Ln[8], core[10];
+    {
+      uint32_t r4[4];
+      sorted_row(wr + 4, r4);                       // row y + 2
+      pair_list(nxt, r4, Ln);                       // rows (y + 1, y + 2)
+      uint32_t in[16];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { in[i] = Lp[i]; in[8 + i] = Ln[i]; }
+      B2D_NET_CORE5(in, core);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) Lp[i] = Ln[i];
+    }
+    uint32_t sl[6], sr[6];
+    {
+      uint32_t in[14], so[4];
+#pragma unroll
+      for (int i = 0; i < 10; ++i) in[i] = core[i];
+      const uint32_t cl[4] = {at(wr + 1, -2), at(wr + 2, -2), at(wr + 3, -2), at(wr + 4, -2)};
+      B2D_NET_SORT4(cl, so);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) in[10 + i] = so[i];
+      B2D_NET_ROW5(in, sl);
+      const uint32_t cr[4] = {at(wr + 1, 3), at(wr + 2, 3), at(wr + 3, 3), at(wr + 4, 3)};
+      B2D_NET_SORT4(cr, so);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) in[10 + i] = so[i];
+      B2D_NET_ROW5(in, sr);
+    }
+    auto finish = [&](const uint32_t (&row4)[4], uint32_t corner, const uint32_t (&surv)[6]) -> uint32_t {
+      uint32_t in10[10], m[2];
+#pragma unroll
+      for (int i = 0; i < 6; ++i) in10[i] = surv[i];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) in10[6 + i] = row4[i];
+      B2D_NET_MID5(in10, m);
+      return VMIN(VMAX(corner, m[0]), m[1]);
+    };
+    uint32_t res[4];
+    {
+      uint32_t t4[4];
+      sorted_row(wr, t4);
+      res[0] = finish(t4, at(wr, -2), sl);
+      res[1] = finish(t4, at(wr, 3), sr);
+      sorted_row(wr + 5, nxt);                      // row y + 3: the next block's row y + 1
+      res[2] = finish(nxt, at(wr + 5, -2), sl);
+      res[3] = finish(nxt, at(wr + 5, 3), sr);
+    }
+#pragma unroll
+    for (int br = 0; br < 2; ++br) {
+      if (2 * k + br >= nrows) break;
+      uint8_t* op = out + (size_t)(2 * k + br) * s.rowbytes;
+      const uint32_t l = res[2 * br], r = res[2 * br + 1];
+      if (v0) op[0] = (uint8_t)l;
+      if (v1) op[3] = (uint8_t)r;
+      if (v2) op[6] = (uint8_t)(l >> 16);
+      if (v3) op[9] = (uint8_t)(r >> 16);
+    }
+  }
+}
+
+cudaError_t launch_median5_sep(const ImageSet& s, cudaStream_t st) {
+  const dim3 grid((s.rowbytes + S7_TILE_WB - 1) / S7_TILE_WB, (s.h + S7_TILE_H - 1) / S7_TILE_H, s.count);
+  k_median5_sep<<<grid, S7_THREADS, (size_t)S5_ROWS * S7_SROW, st>>>(s);
+  count_launch();
+  return cudaGetLastError();
 }
 
 cudaError_t launch_median7_sep(const ImageSet& s, cudaStream_t st) {

@@ -91,7 +91,7 @@ enum {
  *   B2D_A4=0             rows of 4 (mod 8) bytes: group-wise kernel instead of the 32-bit tile / marching kernels
  *   B2D_FILTER_BYTES=1   W % 4 != 0: one-thread-per-byte 3x3 filter instead of the re-aligning tile kernel
  *   B2D_MEDIAN_MODE=1|2|3  median 5 / 7: one-output (1), pair (2) or 2x2-block (3) selection-network kernels instead
- *                        of the default (k = 7: sorted rows merged, b2d_median7.cu; k = 5: 2x2 blocks)
+ *                        of the default (sorted rows merged, b2d_median7.cu)
  *   B2D_BILATERAL=1      bilateral d = 9: the 4 x 1-output kernel of round 1 instead of the 4 x 2-output one
  *   B2D_HAAR=0           db1 / 3 levels: general multi-pass wavelet path instead of the register-resident one
  *   B2D_WV_FUSED=0       general wavelet path: one launch per axis instead of the fused 2-D level kernels

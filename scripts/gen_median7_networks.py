@@ -205,10 +205,62 @@ def main():
                 win = sorted(img[r][c] for r in range(oy, oy + 7) for c in range(ox, ox + 7))
                 assert med == win[24], (trial, oy, ox)
     print("scheme verified on 300 random 8 x 8 neighbourhoods")
+    nets.update(main5())
     if len(sys.argv) > 1 and sys.argv[1] == "--write":
         with open(INC_PATH, "w") as f:
             f.write(render(nets))
         print("wrote", INC_PATH)
+    return nets
+
+
+def main5():
+    """the same scheme for the 5 x 5 median: core 4 x 4 (two row pairs, no 24-list), 16 -> 10 -> (+4) 14 -> 6 -> (+4) two
+    middle values and the corner"""
+    import random
+    nets = {}
+    p = Prog(4)
+    outs = sort_net(p, list(range(4)))
+    for bits in itertools.product((0, 1), repeat=4):
+        v = p.run(bits)
+        assert [v[o] for o in outs] == sorted(bits)
+    nets["SORT4"] = (p, outs)
+    specs = {
+        "PAIR5": ((4, 4), list(range(8))),
+        "CORE5": ((8, 8), list(range(3, 13))),
+        "ROW5": ((10, 4), list(range(4, 10))),
+        "MID5": ((6, 4), [4, 5]),
+    }
+    for name, (sizes, ranks) in specs.items():
+        q, outs = build(sizes, ranks)
+        check_merge(q, outs, sizes, ranks)
+        nets[name] = (q, outs)
+    for name, (q, outs) in nets.items():
+        print("%-6s %3d inputs  %3d ops" % (name, q.n_in, count(q)))
+    n = {k: count(v[0]) for k, v in nets.items()}
+    per_block = (2 * n["SORT4"] + n["PAIR5"]) + n["CORE5"] + 2 * (n["SORT4"] + n["ROW5"]) + \
+        2 * (n["SORT4"] + 2 * (n["MID5"] + 2)) - n["SORT4"]
+    print("5 x 5: min / max operations per 2 x 2 block: %.0f = %.1f per output (forgetful selection: 2 x 79)" %
+          (per_block, per_block / 4))
+    rnd = random.Random(6)
+    for trial in range(300):
+        img = [[rnd.randrange(0, 256 if trial % 2 else 4) for _ in range(6)] for _ in range(6)]   # rows y-2..y+3, cols X-2..X+3
+        def run(name, vals):
+            q, outs = nets[name]
+            v = q.run(vals)
+            return [v[o] for o in outs]
+        cols = [run("SORT4", [img[r][c] for r in range(1, 5)]) for c in range(6)]
+        pairs = [run("PAIR5", cols[c] + cols[c + 1]) for c in (1, 3)]
+        core = run("CORE5", pairs[0] + pairs[1])
+        for oy in (0, 1):
+            outer = run("SORT4", [img[0 if oy == 0 else 5][c] for c in range(1, 5)])
+            surv = run("ROW5", core + outer)
+            for ox in (0, 1):
+                pc = 0 if ox == 0 else 5
+                m4, m5 = run("MID5", surv + cols[pc])
+                med = min(max(img[0 if oy == 0 else 5][pc], m4), m5)
+                win = sorted(img[r][c] for r in range(oy, oy + 5) for c in range(ox, ox + 5))
+                assert med == win[12], (trial, oy, ox)
+    print("5 x 5 scheme verified on 300 random 6 x 6 neighbourhoods")
     return nets
 
 

@@ -24,8 +24,9 @@ def test_networks_are_proven_and_the_include_is_current(capsys):
     finally:
         sys.argv = argv
     out = capsys.readouterr().out
-    assert "scheme verified" in out
+    assert "scheme verified on 300 random 8 x 8" in out and "5 x 5 scheme verified" in out
     with open(g.INC_PATH) as f:
         assert f.read() == g.render(nets), "b2d_median7_nets.inc is stale: python scripts/gen_median7_networks.py --write"
     ops = {k: len(v[0].ops) for k, v in nets.items()}
-    assert ops == {"SORT6": 24, "PAIR": 34, "QUAD": 90, "CORE": 92, "ROW": 46, "MID2": 18}, ops
+    assert ops == {"SORT6": 24, "PAIR": 34, "QUAD": 90, "CORE": 92, "ROW": 46, "MID2": 18,
+                   "SORT4": 10, "PAIR5": 18, "CORE5": 40, "ROW5": 30, "MID5": 14}, ops
