@@ -166,6 +166,7 @@ def main():
         assert [v[o] for o in outs] == sorted(bits)
     nets["SORT6"] = (p, outs)
     specs = {
+        "MERGE33": ((3, 3), list(range(6))),   # SORT6 in the kernel = two 3-sorts (min3, max3, sum - min - max) + this
         "PAIR": ((6, 6), list(range(12))),
         "QUAD": ((12, 12), list(range(24))),
         "CORE": ((12, 24), list(range(11, 25))),

@@ -28,5 +28,5 @@ def test_networks_are_proven_and_the_include_is_current(capsys):
     with open(g.INC_PATH) as f:
         assert f.read() == g.render(nets), "b2d_median7_nets.inc is stale: python scripts/gen_median7_networks.py --write"
     ops = {k: len(v[0].ops) for k, v in nets.items()}
-    assert ops == {"SORT6": 24, "PAIR": 34, "QUAD": 90, "CORE": 92, "ROW": 46, "MID2": 18,
+    assert ops == {"SORT6": 24, "MERGE33": 12, "PAIR": 34, "QUAD": 90, "CORE": 92, "ROW": 46, "MID2": 18,
                    "SORT4": 10, "PAIR5": 18, "CORE5": 40, "ROW5": 30, "MID5": 14}, ops
