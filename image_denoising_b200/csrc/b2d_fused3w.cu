@@ -55,20 +55,20 @@ __device__ __forceinline__ uint2 noise_group(const NoiseArgs& na, int img_local,
 // A4: rows (and image bases) are only 4-byte aligned - rows of 4 (mod 8) bytes, W = 500.  Without a
 // generator (KIND == NK_NONE) groups do not matter, so the same tile code runs with 32-bit accesses.
 template <int KIND, int FILTER, int KW, bool A4 = false>
-__global__ void __launch_bounds__(FT_THREADS, B2D_FT_MINB) k_fused3(ImageSet s, NoiseArgs na) {
+__global__ void __launch_bounds__(FT_THREADS, B2D_FT_MINB) k_fused3(ImageSet s, NoiseArgs na, int th) {
   static_assert(!A4 || KIND == NK_NONE, "the 4-byte aligned variant has no generator");
   using F = Filter3W<FILTER, KW>;
   constexpr int TPB = FT_TWB / (4 * KW);            // threads per band
   constexpr int BANDS = FT_THREADS / TPB;
-  constexpr int BAND_H = FT_TH / BANDS;
+  constexpr int BAND_H = FT_TH / BANDS;             // most rows of a band; this launch's tiles have th <= FT_TH rows
   extern __shared__ __align__(16) uint8_t smem[];
 
   const int tid = threadIdx.x;
   const int c0 = blockIdx.x * FT_TWB;               // first byte column of the tile
-  const int y0 = blockIdx.y * FT_TH;
+  const int y0 = blockIdx.y * th;
   const int img_local = image_of(s, blockIdx.z);
   const uint8_t* img = s.in + (uint64_t)img_local * s.elems;
-  const int rows = min(FT_ROWS, s.h - y0 + 2);      // tile row tr holds image row y0 - 1 + tr
+  const int rows = min(th + 2, s.h - y0 + 2);       // tile row tr holds image row y0 - 1 + tr
 
   // ---- prologue: 16 bytes per thread and step, 4 tile rows per step ----------------
   {
@@ -153,8 +153,9 @@ __global__ void __launch_bounds__(FT_THREADS, B2D_FT_MINB) k_fused3(ImageSet s, 
   // ---- filter: a thread owns KW words of one band and slides down it -----------------
   const int band = tid / TPB, q = tid - band * TPB;
   const int c = c0 + 4 * KW * q;
-  const int o0 = band * BAND_H;                      // first output row (tile-relative) of the band
-  const int nrows = min(BAND_H, s.h - y0 - o0);
+  const int band_h = th / BANDS;
+  const int o0 = band * band_h;                      // first output row (tile-relative) of the band
+  const int nrows = min(band_h, s.h - y0 - o0);
   if (c >= s.rowbytes || nrows <= 0) return;
   const uint8_t* sp = smem + FT_APRON + 4 * KW * q + o0 * FT_SROW;
   auto load_row = [&](int tr, typename F::Part& p) {
@@ -212,8 +213,23 @@ static cudaError_t launch_one(const ImageSet& s, const NoiseArgs& na, cudaStream
     if (e != cudaSuccess) return e;
     attr_done[dev & 63] = true;
   }
-  const dim3 grid((s.rowbytes + FT_TWB - 1) / FT_TWB, (s.h + FT_TH - 1) / FT_TH, s.count);
-  k_fused3<KIND, FILTER, KW, A4><<<grid, FT_THREADS, FT_SMEM, st>>>(s, na);
+  // Tile height: FT_TH, except for batches of a few waves of CTAs, where the last, nearly empty wave decides (BASELINE
+  // config 1: 16 images = 624 tiles of 48 rows on 592 slots = two waves for 1.05 waves of work).  Cost model: waves x
+  // (rows generated per tile + 6 for the tile's fixed cost); multiples of 4 so that 2 or 4 bands divide the tile.  For
+  // large batches this picks FT_TH (fewer apron rows), which is also what was measured best (profiles/r02r_tile_geometry.txt).
+  const long slots = (long)sm_count() * B2D_FT_MINB;
+  const long cols = (s.rowbytes + FT_TWB - 1) / FT_TWB;
+  int th = FT_TH;
+  if (cols * ((s.h + FT_TH - 1) / FT_TH) * s.count <= 6 * slots) {
+    long best = -1;
+    for (int t = FT_TH; t >= 16; t -= 4) {
+      const long ctas = cols * ((s.h + t - 1) / t) * s.count;
+      const long cost = ((ctas + slots - 1) / slots) * (t + 8);
+      if (best < 0 || cost < best) { best = cost; th = t; }
+    }
+  }
+  const dim3 grid((unsigned)cols, (s.h + th - 1) / th, s.count);
+  k_fused3<KIND, FILTER, KW, A4><<<grid, FT_THREADS, FT_SMEM, st>>>(s, na, th);
   count_launch();
   return cudaGetLastError();
 }
