@@ -46,6 +46,29 @@ def test_quant_injected_centres_bit_exact(cuda, shape, k, den):
         assert np.array_equal(got[i], want), (spec, shape, i, int((got[i] != want).sum()))
 
 
+@pytest.mark.parametrize("case", ["near_ties", "wild_centre"])
+def test_quant_label_decision_paths(cuda, case):
+    """The label is decided by fp32 scores unless the two best centres are within 0.25 of a tie (then the exact float64
+    loop in NumPy's operation order runs) or a centre lies far outside the uint8 cube (then only the exact loop runs):
+    centres that differ by 1e-9 / 1e-4 force the first case on every pixel, a centre at 600 the second."""
+    from image_denoising_b200 import api
+    batch = synth_batch(2, 96, 128, seed=31, kind="smooth")
+    rng = np.random.RandomState(4)
+    if case == "near_ties":                                               # k = 10: every pixel has two or three near-equal bests
+        base = np.stack([rng.uniform(20, 235, 4), rng.uniform(100, 160, 4), rng.uniform(100, 160, 4)], -1)
+        centres = np.concatenate([base + 1e-4, base, base[:2] - 1e-9], 0)
+    else:                                                                 # k = 7
+        base = np.stack([rng.uniform(20, 235, 6), rng.uniform(100, 160, 6), rng.uniform(100, 160, 6)], -1)
+        centres = np.concatenate([base, [[600.0, 128.0, 128.0]]], 0)
+    k = len(centres)
+    spec = "quant_var%d" % k
+    f0 = torch.from_numpy(np.stack([centres, centres[::-1].copy()])).to(cuda).contiguous()
+    got = api.apply(torch.from_numpy(batch).to(cuda), spec, fields=(f0, None)).cpu().numpy()
+    for i, cen in enumerate([centres, centres[::-1].copy()]):
+        want = C.corrupt(batch[i], spec, fields={"centers": cen})
+        assert np.array_equal(got[i], want), (case, i, int((got[i] != want).sum()))
+
+
 def _inertia(img, out):
     import cv2
     lab = cv2.cvtColor(img, cv2.COLOR_BGR2LAB).reshape(-1, 3).astype(np.float64)
