@@ -144,6 +144,19 @@ int run_group(const RunCtx& c, const SpecGroup& g, int lo, int hi) {
       ba.chunk_sums = reinterpret_cast<double*>(c.ws + p->off_scan);
       ba.nchunks = p->brown_chunks;
       ba.field = c.ws + p->off_aux;
+      ba.add_out = nullptr;
+      // Consumers other than the fused 3x3 kernels and the wavelet (median 5 / 7, bilateral, none) read a corrupted uint8
+      // image: the field kernel adds the image itself and writes that - no field in HBM, no separate table-add pass.
+      const bool direct = sp.denoise != B2D_DENOISE_WAVELET &&
+                          (filter3_kind(sp) == FK_NONE || !word_aligned(p, s.in, s.out));
+      if (direct) {
+        ba.add_out = sp.denoise == B2D_DENOISE_NONE ? c.out : stage;
+        CK(launch_brownian_field(s, na, ba, inject, c.st));
+        if (sp.denoise == B2D_DENOISE_NONE || c.defer_denoise) return B2D_OK;
+        ImageSet ds = s;
+        ds.in = stage;
+        return denoise_u8(c, sp, ds);
+      }
       CK(launch_brownian_field(s, na, ba, inject, c.st));
       na.tab = ba.field;
       na.tab_stride = p->elems;

@@ -199,7 +199,8 @@ __global__ void __launch_bounds__(BR_THREADS) k_brown_field(ImageSet s, NoiseArg
   for (int i = 0; i < 8; ++i) sum += d[i];
   double total;
   double b = block_exclusive_scan(sum, &total) + ba.chunk_sums[(uint64_t)img_local * ba.nchunks + blockIdx.x];
-  uint8_t* f = ba.field + (uint64_t)img_local * na.elems;
+  uint8_t* f = (ba.add_out ? ba.add_out : ba.field) + (uint64_t)img_local * na.elems;
+  const uint8_t* img = ba.add_out ? s.in + (uint64_t)img_local * s.elems : nullptr;
   uint32_t v[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
@@ -207,12 +208,18 @@ __global__ void __launch_bounds__(BR_THREADS) k_brown_field(ImageSet s, NoiseArg
     b += d[i];
   }
   const uint64_t e = (uint64_t)g * 8u;
-  if (e + 8u <= na.elems && ((reinterpret_cast<uintptr_t>(f + e) & 7u) == 0)) {
-    *reinterpret_cast<uint2*>(f + e) = make_uint2(pack4(v[0], v[1], v[2], v[3]), pack4(v[4], v[5], v[6], v[7]));
+  if (e + 8u <= na.elems && ((reinterpret_cast<uintptr_t>(f + e) & 7u) == 0) &&
+      (!img || (reinterpret_cast<uintptr_t>(img + e) & 7u) == 0)) {
+    uint2 w = make_uint2(pack4(v[0], v[1], v[2], v[3]), pack4(v[4], v[5], v[6], v[7]));
+    if (img) {                             // cv2.add(img, field): saturating, minibatch.py:828
+      const uint2 x = __ldg(reinterpret_cast<const uint2*>(img + e));
+      w = make_uint2(__vaddus4(x.x, w.x), __vaddus4(x.y, w.y));
+    }
+    *reinterpret_cast<uint2*>(f + e) = w;
   } else {
 #pragma unroll
     for (int i = 0; i < 8; ++i)
-      if (e + i < na.elems) f[e + i] = (uint8_t)v[i];
+      if (e + i < na.elems) f[e + i] = (uint8_t)(img ? min(v[i] + (uint32_t)img[e + i], 255u) : v[i]);
   }
 }
 

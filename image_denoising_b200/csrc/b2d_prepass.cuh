@@ -9,6 +9,9 @@ struct BrownianArgs {
   double* chunk_sums;   // [batch][nchunks] workspace
   uint32_t nchunks;
   uint8_t* field;       // [batch][elems] u8 noise field (batch-indexed)
+  // non-null: the field kernel writes cv2.add(image, field) (saturating) here instead of the field - the corrupted
+  // image in one step, for the consumers that are not the fused 3x3 kernels ([batch][elems], batch-indexed like s.in)
+  uint8_t* add_out;
 };
 
 uint32_t brownian_chunks(uint64_t elems);
