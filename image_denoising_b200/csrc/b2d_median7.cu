@@ -15,7 +15,8 @@
 //   level 2 : survivors + the sorted outer column (20 values): the 6 smallest / largest go the same way -> 8 survivors.
 //   level 3 : survivors + the sorted private row (its 6 core columns, reused as the next block's new core row) = 14
 //             values, whose two middle ones m6 <= m7 bracket the median of the 15: min(max(corner, m6), m7).
-// 463 min / max instructions per block = 116 per output byte instead of 362 (+ the operand fetches).  All programs are
+// 463 min / max operations per block = 116 per output byte instead of 362 (443 instructions with the 3-input sorts
+// below; + the operand fetches).  All programs are
 // generated and PROVEN (0-1 principle over every sorted input) by scripts/gen_median7_networks.py
 // (b2d_median7_nets.inc); data independent, so they run on the two u16 lanes of a register: lane 0 = the block at byte
 // column c, lane 1 = the block 6 bytes (2 pixels) to the right.  Border: REPLICATE, as OpenCV's medianBlur.
@@ -47,7 +48,7 @@ constexpr int S7_SEGS = 2;                         // vertical segments per tile
 constexpr int S7_SEG_H = 24;                       // rows per segment = 12 steps of the march
 constexpr int S7_THREADS = S7_XU * 3 * S7_SEGS;    // 192
 constexpr int S7_TILE_WB = S7_XU * 12;             // 384 bytes
-constexpr int S7_TILE_H = S7_SEGS * S7_SEG_H;      // 32 rows
+constexpr int S7_TILE_H = S7_SEGS * S7_SEG_H;      // 48 rows
 constexpr int S7_APRON = 12;                       // >= 9 bytes to the left, 9 beyond the unit to the right; multiple of 4
 constexpr int S7_SROW = S7_TILE_WB + 2 * S7_APRON;
 constexpr int S7_ROWS = S7_TILE_H + 7;             // rows y0 - 3 .. y0 + TILE_H + 3 (the last block reads row y + 4)
