@@ -171,34 +171,32 @@ __global__ void __launch_bounds__(BR_THREADS) k_brown_chunksum(ImageSet s, Noise
   if (threadIdx.x == 0) ba.chunk_sums[(uint64_t)img_local * ba.nchunks + blockIdx.x] = total;
 }
 
-// exclusive scan of one image's chunk sums, in place: one CTA per image, a thread adds up its run of consecutive chunks,
-// the runs are scanned across the CTA (round 1 ran ONE thread per image over all ~900 chunks: 0.24 ms per 512 images
-// on 8 CTAs)
+// exclusive scan of one image's chunk sums, in place, in SEQUENTIAL order (((t0 + t1) + t2) + ...: the order in which
+// k_brown_march below accumulates them, so that both paths give the same bits).  One warp per image: 32 sums are loaded
+// at once, every lane replays the 32 additions (round 1 ran one THREAD per image on 8 CTAs: 0.24 ms per 512 images).
 __global__ void __launch_bounds__(BR_THREADS) k_brown_scan(ImageSet s, BrownianArgs ba) {
-  double* cs = ba.chunk_sums + (uint64_t)image_of(s, blockIdx.x) * ba.nchunks;
-  const uint32_t per = (ba.nchunks + BR_THREADS - 1) / BR_THREADS;
-  const uint32_t k0 = min(threadIdx.x * per, ba.nchunks), k1 = min(k0 + per, ba.nchunks);
-  double sum = 0.0;
-  for (uint32_t k = k0; k < k1; ++k) sum += cs[k];
-  double total;
-  double run = block_exclusive_scan(sum, &total);
-  for (uint32_t k = k0; k < k1; ++k) {
-    const double t = cs[k];
-    cs[k] = run;
-    run += t;
+  const int z = blockIdx.x * (BR_THREADS / 32) + (threadIdx.x >> 5);
+  if (z >= s.count) return;
+  const int lane = threadIdx.x & 31;
+  double* cs = ba.chunk_sums + (uint64_t)image_of(s, z) * ba.nchunks;
+  double run = 0.0;
+  for (uint32_t base = 0; base < ba.nchunks; base += 32) {
+    const double v = base + lane < ba.nchunks ? cs[base + lane] : 0.0;
+    double mine = 0.0;
+#pragma unroll 8
+    for (int j = 0; j < 32; ++j) {
+      const double x = __shfl_sync(0xffffffffu, v, j);
+      if (lane == j) mine = run;
+      run = __dadd_rn(run, x);
+    }
+    if (base + lane < ba.nchunks) cs[base + lane] = mine;
   }
 }
 
-template <bool INJECT>
-__global__ void __launch_bounds__(BR_THREADS) k_brown_field(ImageSet s, NoiseArgs na, BrownianArgs ba) {
-  const int img_local = image_of(s, blockIdx.z);
-  const uint32_t g = blockIdx.x * BR_THREADS + threadIdx.x;
-  double d[8], sum = 0.0;
-  brownian_steps<INJECT>(na, ba, img_local, g, d);
-#pragma unroll
-  for (int i = 0; i < 8; ++i) sum += d[i];
-  double total;
-  double b = block_exclusive_scan(sum, &total) + ba.chunk_sums[(uint64_t)img_local * ba.nchunks + blockIdx.x];
+// one chunk of the field: the thread's 8 steps d (their sum already scanned inside the CTA: b = B at the thread's first
+// element) -> (B * 255) -> u8, or cv2.add(image, that) when add_out is set
+__device__ __forceinline__ void brownian_write(const ImageSet& s, const NoiseArgs& na, const BrownianArgs& ba, int img_local,
+                                               uint32_t g, const double (&d)[8], double b) {
   uint8_t* f = (ba.add_out ? ba.add_out : ba.field) + (uint64_t)img_local * na.elems;
   const uint8_t* img = ba.add_out ? s.in + (uint64_t)img_local * s.elems : nullptr;
   uint32_t v[8];
@@ -223,14 +221,55 @@ __global__ void __launch_bounds__(BR_THREADS) k_brown_field(ImageSet s, NoiseArg
   }
 }
 
+template <bool INJECT>
+__global__ void __launch_bounds__(BR_THREADS) k_brown_field(ImageSet s, NoiseArgs na, BrownianArgs ba) {
+  const int img_local = image_of(s, blockIdx.z);
+  const uint32_t g = blockIdx.x * BR_THREADS + threadIdx.x;
+  double d[8], sum = 0.0;
+  brownian_steps<INJECT>(na, ba, img_local, g, d);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) sum += d[i];
+  double total;
+  const double b = block_exclusive_scan(sum, &total) + ba.chunk_sums[(uint64_t)img_local * ba.nchunks + blockIdx.x];
+  brownian_write(s, na, ba, img_local, g, d, b);
+}
+
+// Large batches: ONE CTA per image walks the image's chunks in order and carries the running sum - the normals are
+// generated once (no chunk-sum pass, no scan).  Same arithmetic as the three kernels: per chunk the same block scan, across
+// chunks the same sequential additions.  Used when the batch alone fills the GPU (>= 2 images per SM).
+template <bool INJECT>
+__global__ void __launch_bounds__(BR_THREADS) k_brown_march(ImageSet s, NoiseArgs na, BrownianArgs ba) {
+  const int img_local = image_of(s, blockIdx.x);
+  double run = 0.0;
+  for (uint32_t chunk = 0; chunk < ba.nchunks; ++chunk) {
+    const uint32_t g = chunk * BR_THREADS + threadIdx.x;
+    double d[8], sum = 0.0;
+    brownian_steps<INJECT>(na, ba, img_local, g, d);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) sum += d[i];
+    double total;
+    const double b = block_exclusive_scan(sum, &total) + run;
+    brownian_write(s, na, ba, img_local, g, d, b);
+    run = __dadd_rn(run, total);
+  }
+}
+
 cudaError_t launch_brownian_field(const ImageSet& s, const NoiseArgs& na, const BrownianArgs& ba, bool inject,
                                   cudaStream_t st) {
   if (s.count <= 0) return cudaSuccess;
+  static const char* march_env = knob("B2D_BROWN_MARCH");           // 0 / 1 forces one of the two paths (cross-check)
+  const bool march = march_env ? march_env[0] == '1' : s.count >= 2 * sm_count();
+  if (march) {
+    if (inject) k_brown_march<true><<<s.count, BR_THREADS, 0, st>>>(s, na, ba);
+    else k_brown_march<false><<<s.count, BR_THREADS, 0, st>>>(s, na, ba);
+    count_launch();
+    return cudaGetLastError();
+  }
   const dim3 grid(ba.nchunks, 1, s.count);
   if (inject) k_brown_chunksum<true><<<grid, BR_THREADS, 0, st>>>(s, na, ba);
   else k_brown_chunksum<false><<<grid, BR_THREADS, 0, st>>>(s, na, ba);
   count_launch();
-  k_brown_scan<<<s.count, BR_THREADS, 0, st>>>(s, ba);
+  k_brown_scan<<<(s.count + BR_THREADS / 32 - 1) / (BR_THREADS / 32), BR_THREADS, 0, st>>>(s, ba);
   count_launch();
   if (inject) k_brown_field<true><<<grid, BR_THREADS, 0, st>>>(s, na, ba);
   else k_brown_field<false><<<grid, BR_THREADS, 0, st>>>(s, na, ba);

@@ -88,6 +88,7 @@ enum {
 /* Diagnostic environment variables.  They select cross-check kernels inside b2d_run / b2d_run_host and
  * are honoured ONLY when B2D_DEBUG_KNOBS=1 is also set (read once per process); otherwise ignored.
  *   B2D_MARCH=0|1        3x3 filters: force the tile kernel (0) or the row-marching kernel (1)
+ *   B2D_BROWN_MARCH=0|1  brownian: chunk-sum / scan / field kernels (0) or one CTA per image (1) whatever the batch size
  *   B2D_A4=0             rows of 4 (mod 8) bytes: group-wise kernel instead of the 32-bit tile / marching kernels
  *   B2D_FILTER_BYTES=1   W % 4 != 0: one-thread-per-byte 3x3 filter instead of the re-aligning tile kernel
  *   B2D_MEDIAN_MODE=1|2|3  median 5 / 7: one-output (1), pair (2) or 2x2-block (3) selection-network kernels instead

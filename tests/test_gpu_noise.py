@@ -137,6 +137,19 @@ def test_batch_split_and_seed_semantics(cuda):
     assert torch.equal(full, two)
 
 
+@pytest.mark.parametrize("spec", ["brownian_var0.09", "brownian_median_var0.09", "brownian_mean_var0.09"])
+def test_brownian_large_batch_path_equals_small_batch_path(cuda, spec):
+    """A batch of >= 2 images per SM takes the one-CTA-per-image brownian kernel (running sum carried through the image's
+    chunks), smaller batches the chunk-sums / scan / field kernels: same arithmetic, so the same bytes whichever way a
+    batch is cut (odd size: chunks end inside rows, images start at odd addresses)."""
+    from image_denoising_b200 import api
+    n = 2 * torch.cuda.get_device_properties(cuda).multi_processor_count + 5
+    batch = torch.from_numpy(np.concatenate([synth_batch(7, 45, 61, seed=9, kind="smooth")] * (n // 7 + 1))[:n]).to(cuda)
+    full = api.apply(batch, spec, seed=3, ksize=5)
+    parts = [api.apply(batch[i:i + 100].contiguous(), spec, seed=3, first_index=i, ksize=5) for i in range(0, n, 100)]
+    assert torch.equal(full, torch.cat(parts))
+
+
 @pytest.mark.parametrize("spec", ["gaussian_original_var1.0", "sap_original_var0.4", "speckle_original_var1.0",
                                   "sap_mean_var0.4", "gaussian_median_var1.0"])
 def test_unaligned_image_base_same_bytes(cuda, spec):
